@@ -1,0 +1,241 @@
+/*
+ * nxs_classify.h — C ABI of the B200 failure-classification library.
+ *
+ * This is the drop-in boundary for ONE path of SneaksAndData/nexus-supervisor:
+ * the event classifier `(*Supervisor).onEvent` (services/supervisor.go:137-259)
+ * followed by the decision part of `(*Supervisor).superviseAction`
+ * (services/supervisor.go:261-374), applied to a batch of event records that the
+ * host has flattened into struct-of-arrays columns.  The reference exposes no
+ * FFI of its own (it is pure Go, CGO_ENABLED=0); the entry points below are what
+ * a cgo shim next to services/supervisor.go would bind.
+ *
+ * Conventions
+ *   - every function returns 0 (NXS_OK) or a negative nxs_status; nothing aborts
+ *     or throws across the boundary; nxs_strerror() names a status;
+ *   - plain pointers and sizes only; the caller owns every buffer and the library
+ *     reads/writes it only during the call (for *_device calls: until the ctx
+ *     stream reaches the end of the work the call enqueued);
+ *   - a ctx belongs to one GPU and one caller thread at a time;
+ *   - there is no CPU fallback: without a CUDA device nxs_create fails.
+ *
+ * All citations `services/...:N` are relative to the reference repository.
+ */
+#ifndef NXS_CLASSIFY_H
+#define NXS_CLASSIFY_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NXS_ABI_VERSION 1
+
+/* ---------------------------------------------------------------- status */
+typedef enum nxs_status {
+  NXS_OK = 0,
+  NXS_ERR_ARG = -1,       /* null pointer, misaligned column, bad enum       */
+  NXS_ERR_CAPACITY = -2,  /* n exceeds the ctx capacity / 2^32-2 records     */
+  NXS_ERR_CUDA = -3,      /* a CUDA runtime call failed (see nxs_last_error) */
+  NXS_ERR_NO_DEVICE = -4, /* no usable CUDA device: there is no CPU fallback */
+  NXS_ERR_NOMEM = -5,
+  NXS_ERR_UNKNOWN_ACTION = -6 /* services/supervisor.go:371-372              */
+} nxs_status;
+
+/* ------------------------------------------------- interned vocabularies */
+/* event.InvolvedObject.Kind (services/supervisor.go:159,210) */
+enum { NXS_KIND_OTHER = 0, NXS_KIND_JOB = 1, NXS_KIND_POD = 2 };
+
+/* event.Reason, interned.  1..7 are the seven reasons the two switches handle
+ * (services/supervisor.go:171-207 and :223-257); the rest are common kubelet /
+ * job-controller reasons that fall into `default`.  0 and every id >= 32 are
+ * "unknown" and also fall into `default`. */
+enum {
+  NXS_REASON_UNKNOWN = 0,
+  NXS_REASON_FAILED_CREATE = 1,          /* Job, :172 */
+  NXS_REASON_DEADLINE_EXCEEDED = 2,      /* Job, :183 */
+  NXS_REASON_BACKOFF_LIMIT_EXCEEDED = 3, /* Job, :183 */
+  NXS_REASON_POD_FAILURE_POLICY = 4,     /* Job, :194 */
+  NXS_REASON_STARTED = 5,                /* Pod, :224 */
+  NXS_REASON_FAILED = 6,                 /* Pod, :234 */
+  NXS_REASON_BACKOFF = 7,                /* Pod, :244 */
+  NXS_REASON_SCHEDULED = 8,
+  NXS_REASON_PULLING = 9,
+  NXS_REASON_PULLED = 10,
+  NXS_REASON_CREATED = 11,
+  NXS_REASON_KILLING = 12,
+  NXS_REASON_SUCCESSFUL_CREATE = 13,
+  NXS_REASON_COMPLETED = 14,
+  NXS_REASON_FAILED_SCHEDULING = 15,
+  NXS_REASON_LUT_SIZE = 32
+};
+
+/* checkpoint.LifecycleStage as an id (strings live in nexus-core, host-side) */
+enum {
+  NXS_STAGE_NEW = 0,
+  NXS_STAGE_BUFFERED = 1,
+  NXS_STAGE_RUNNING = 2,
+  NXS_STAGE_COMPLETED = 3,
+  NXS_STAGE_FAILED = 4,
+  NXS_STAGE_SCHEDULING_FAILED = 5,
+  NXS_STAGE_DEADLINE_EXCEEDED = 6,
+  NXS_STAGE_CANCELLED = 7
+};
+
+/* Default for the unpinned nexus-core predicate `IsFinished()`
+ * (services/supervisor.go:276): bit s set <=> stage s counts as finished.
+ * Pinned by the reference test: CANCELLED finished, BUFFERED/RUNNING not. */
+#define NXS_FINISHED_MASK_DEFAULT                                            \
+  ((uint16_t)((1u << NXS_STAGE_COMPLETED) | (1u << NXS_STAGE_FAILED) |       \
+              (1u << NXS_STAGE_SCHEDULING_FAILED) |                          \
+              (1u << NXS_STAGE_DEADLINE_EXCEEDED) | (1u << NXS_STAGE_CANCELLED)))
+
+/* DecisionAction (services/supervisor.go:49-56) */
+enum {
+  NXS_ACTION_NONE = 0,
+  NXS_ACTION_STUCK_IN_PENDING = 1,  /* ToFailStuckInPending   */
+  NXS_ACTION_FATAL_ERROR = 2,       /* ToFailFatalError       */
+  NXS_ACTION_DEADLINE_EXCEEDED = 3, /* ToFailDeadlineExceeded */
+  NXS_ACTION_RUNNING = 4            /* ToRunning              */
+};
+
+/* flags column */
+#define NXS_FLAG_SUPERVISED 0x01u /* resolvers.IsNexusRunEvent, :147-157      */
+#define NXS_FLAG_FOUND 0x02u      /* resolvers.GetCachedObject != nil, :160/211 */
+#define NXS_FLAG_CHECKPOINT 0x04u /* ReadCheckpoint succeeded, :264-273       */
+
+/* ---------------------------------------------------------------- verdict
+ * One u32 per record and one per job row.
+ *   bits  0-2  action        DecisionAction id
+ *   bits  3-6  new_stage     stage id written by the upsert (0 unless upsert)
+ *   bits  7-8  cause_tpl     nxs_cause_template index (0 = cause untouched)
+ *   bits  9-11 msg_tpl       nxs_msg_template index (RunStatusMessage)
+ *   bit   12   delete_job    Jobs(ns).Delete issued (:268,:289,:314,:339)
+ *   bit   13   upsert        UpsertCheckpoint issued (:301,:328,:353,:364)
+ *   bit   14   skip_finished IsFinished() no-op (:276-279)
+ *   bits 15-16 err           1 = no checkpoint (:265-273), 2 = unknown action
+ */
+#define NXS_V_ACTION(v) ((uint32_t)(v) & 7u)
+#define NXS_V_NEW_STAGE(v) (((uint32_t)(v) >> 3) & 15u)
+#define NXS_V_CAUSE_TPL(v) (((uint32_t)(v) >> 7) & 3u)
+#define NXS_V_MSG_TPL(v) (((uint32_t)(v) >> 9) & 7u)
+#define NXS_V_DELETE_JOB(v) (((uint32_t)(v) >> 12) & 1u)
+#define NXS_V_UPSERT(v) (((uint32_t)(v) >> 13) & 1u)
+#define NXS_V_SKIP_FINISHED(v) (((uint32_t)(v) >> 14) & 1u)
+#define NXS_V_ERR(v) (((uint32_t)(v) >> 15) & 3u)
+#define NXS_V_PACK(action, stage, cause, msg, del, ups, skip, err)           \
+  ((uint32_t)(action) | ((uint32_t)(stage) << 3) | ((uint32_t)(cause) << 7) | \
+   ((uint32_t)(msg) << 9) | ((uint32_t)(del) << 12) | ((uint32_t)(ups) << 13) | \
+   ((uint32_t)(skip) << 14) | ((uint32_t)(err) << 15))
+#define NXS_ERR_NO_CHECKPOINT 1u
+#define NXS_NO_WINNER 0xFFFFFFFFu
+
+/* Per-job row: the outcome of replaying, in record order, every record of one
+ * job against its checkpoint row — what the reference does one event at a time
+ * through ReadCheckpoint / IsFinished / switch / UpsertCheckpoint
+ * (services/supervisor.go:264-370).  Records of a job must be adjacent.
+ *   verdict.action     action of the LAST applied record (decides the stage)
+ *   verdict.new_stage  resulting lifecycle stage (if upsert)
+ *   verdict.cause_tpl / msg_tpl  from the winner = the last applied record
+ *                      with a failure action; its message/trace become
+ *                      algorithm_failure_cause / _details (:298-299,:325-326,:350-351)
+ *   verdict.delete_job / upsert / skip_finished / err   OR over the records
+ *   winner_idx         record index of the winner in this batch, NXS_NO_WINNER if none
+ */
+typedef struct nxs_job_row {
+  uint64_t job_key;
+  uint32_t verdict;
+  uint32_t winner_idx;
+} nxs_job_row;
+
+/* Input columns, one element per event record. */
+typedef struct nxs_batch {
+  const uint8_t *kind;       /* NXS_KIND_*                                   */
+  const uint16_t *reason_id; /* NXS_REASON_*                                 */
+  const uint8_t *flags;      /* NXS_FLAG_*                                   */
+  const uint8_t *cur_stage;  /* NXS_STAGE_* of the row ReadCheckpoint gave   */
+  const uint64_t *job_key;   /* hash of (algorithm, id) — the checkpoint PK  */
+  uint64_t n;                /* records; < 2^32 - 1                          */
+} nxs_batch;
+
+typedef struct nxs_out {
+  uint32_t *verdict;     /* n                                               */
+  nxs_job_row *job_rows; /* capacity >= number of jobs (n is always enough) */
+  uint64_t *n_jobs;      /* 1 element                                       */
+} nxs_out;
+
+typedef struct nxs_ctx nxs_ctx;
+
+/* ------------------------------------------------------------ life cycle */
+/* Replaces the per-Supervisor state built in NewSupervisor/Init
+ * (services/supervisor.go:69-135): one ctx per (GPU, caller thread).
+ * `finished_mask` stands in for nexus-core's IsFinished() (:276). */
+int nxs_create(int device, uint64_t max_records, uint16_t finished_mask,
+               nxs_ctx **out);
+void nxs_destroy(nxs_ctx *ctx);
+/* Use an existing cudaStream_t (passed as void*) instead of the ctx's own. */
+int nxs_set_stream(nxs_ctx *ctx, void *cuda_stream);
+int nxs_sync(nxs_ctx *ctx);
+const char *nxs_strerror(int status);
+const char *nxs_last_error(const nxs_ctx *ctx);
+int nxs_abi_version(void);
+
+/* ------------------------------------------------------------- hot path */
+/* onEvent + superviseAction decision for a batch (services/supervisor.go:137-374).
+ * Host pointers; copies in, classifies on the GPU, copies verdicts, job rows and
+ * the job count back before returning. */
+int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out);
+/* Same with DEVICE pointers (16-byte aligned columns); asynchronous on the ctx
+ * stream.  out->n_jobs is a device pointer too. */
+int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *d_in,
+                        const nxs_out *d_out);
+/* Number of kernels the ctx has launched so far (bench.py's gpu_launches). */
+uint64_t nxs_launch_count(const nxs_ctx *ctx);
+
+/* pinned host memory for nxs_classify callers */
+int nxs_alloc_host(size_t bytes, void **out);
+void nxs_free_host(void *p);
+
+/* --------------------------------------------------- host-side vocabulary */
+/* Interning used by the host flattening layer: what the Go side would do with
+ * event.InvolvedObject.Kind / event.Reason before filling the columns. */
+uint8_t nxs_intern_kind(const char *s, size_t len);
+uint16_t nxs_intern_reason(const char *s, size_t len);
+const char *nxs_reason_name(uint32_t reason_id);
+const char *nxs_action_name(uint32_t action); /* :52-55 */
+const char *nxs_stage_name(uint32_t stage);
+/* RunStatusMessage texts (:176,:187,:198,:227,:237,:247); idx 0 = "" */
+const char *nxs_msg_template(uint32_t idx);
+/* AlgorithmFailureCause formats (:298,:325,:350); idx 0 = NULL (untouched) */
+const char *nxs_cause_template(uint32_t idx);
+
+/* ------------------------------------------------------------- sharding */
+/* Shard of a job for a G-GPU run: splitmix64(job_key) % n_shards. */
+uint32_t nxs_shard_of(uint64_t job_key, uint32_t n_shards);
+
+/* ------------------------------------------------- synthetic workloads */
+enum { NXS_WORKLOAD_UNIFORM = 1, NXS_WORKLOAD_SKEWED = 2 };
+#define NXS_DEFAULT_SEED 0x6E65787573ull
+/* Writable view of the input columns (device pointers). */
+typedef struct nxs_columns {
+  uint8_t *kind;
+  uint16_t *reason_id;
+  uint8_t *flags;
+  uint8_t *cur_stage;
+  uint64_t *job_key;
+  uint64_t capacity;
+} nxs_columns;
+/* Fill device columns with records [first, first+n) of the counter-based
+ * synthetic stream (bench / test input; the oracle regenerates the same stream
+ * on the CPU).  With n_shards > 1 only records whose job falls in `shard` are
+ * kept, compacted in stream order; *n_kept (host pointer) receives the count. */
+int nxs_generate_device(nxs_ctx *ctx, int workload, uint64_t seed,
+                        uint64_t first, uint64_t n, uint32_t shard,
+                        uint32_t n_shards, const nxs_columns *d_cols,
+                        uint64_t *n_kept);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NXS_CLASSIFY_H */

@@ -1,0 +1,159 @@
+"""Classifier — thin host wrapper over the C ABI (include/nxs_classify.h).
+
+`Classifier.classify` takes host (numpy) columns, `Classifier.classify_device`
+takes device pointers (e.g. torch CUDA tensors) and is asynchronous on the
+stream given to the constructor.  Both go through libnxs_classify.so.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi
+
+JOB_ROW = np.dtype([("job_key", "<u8"), ("verdict", "<u4"), ("winner_idx", "<u4")])
+
+KIND = {"Other": 0, "Job": 1, "Pod": 2}
+REASON = {"Unknown": 0, "FailedCreate": 1, "DeadlineExceeded": 2, "BackoffLimitExceeded": 3, "PodFailurePolicy": 4,
+          "Started": 5, "Failed": 6, "BackOff": 7, "Scheduled": 8, "Pulling": 9, "Pulled": 10, "Created": 11,
+          "Killing": 12, "SuccessfulCreate": 13, "Completed": 14, "FailedScheduling": 15}
+STAGE = {"NEW": 0, "BUFFERED": 1, "RUNNING": 2, "COMPLETED": 3, "FAILED": 4, "SCHEDULING_FAILED": 5,
+         "DEADLINE_EXCEEDED": 6, "CANCELLED": 7}
+ACTION = {"": 0, "ToFailStuckInPending": 1, "ToFailFatalError": 2, "ToFailDeadlineExceeded": 3, "ToRunning": 4}
+FLAG_SUPERVISED, FLAG_FOUND, FLAG_CHECKPOINT = 1, 2, 4
+FINISHED_MASK_DEFAULT = sum(1 << STAGE[s] for s in
+                            ("COMPLETED", "FAILED", "SCHEDULING_FAILED", "DEADLINE_EXCEEDED", "CANCELLED"))
+NO_WINNER = 0xFFFFFFFF
+WORKLOAD_UNIFORM, WORKLOAD_SKEWED = 1, 2
+DEFAULT_SEED = 0x6E65787573
+
+
+class NxsError(RuntimeError):
+    def __init__(self, status, detail=""):
+        self.status = status
+        msg = _abi.load().nxs_strerror(status).decode()
+        super().__init__(f"nxs error {status} ({msg})" + (f": {detail}" if detail else ""))
+
+
+def unpack_verdict(v):
+    """Packed u32 verdict -> dict of fields (include/nxs_classify.h bit layout)."""
+    v = int(v)
+    return {"action": v & 7, "new_stage": (v >> 3) & 15, "cause_tpl": (v >> 7) & 3, "msg_tpl": (v >> 9) & 7,
+            "delete_job": (v >> 12) & 1, "upsert": (v >> 13) & 1, "skip_finished": (v >> 14) & 1,
+            "err": (v >> 15) & 3}
+
+
+def shard_of(job_key, n_shards):
+    return _abi.load().nxs_shard_of(int(job_key), int(n_shards))
+
+
+def intern_kind(s):
+    b = s.encode()
+    return _abi.load().nxs_intern_kind(b, len(b))
+
+
+def intern_reason(s):
+    b = s.encode()
+    return _abi.load().nxs_intern_reason(b, len(b))
+
+
+def msg_template(i):
+    return _abi.load().nxs_msg_template(i).decode()
+
+
+def cause_template(i):
+    t = _abi.load().nxs_cause_template(i)
+    return None if t is None else t.decode()
+
+
+def stage_name(i):
+    return _abi.load().nxs_stage_name(i).decode()
+
+
+def action_name(i):
+    return _abi.load().nxs_action_name(i).decode()
+
+
+def reason_name(i):
+    return _abi.load().nxs_reason_name(i).decode()
+
+
+class Classifier:
+    """One nxs_ctx: a GPU, a stream and the scratch the kernel needs."""
+
+    def __init__(self, device=0, max_records=1 << 20, finished_mask=FINISHED_MASK_DEFAULT, stream=None):
+        self._lib = _abi.load()
+        self._ctx = C.c_void_p()
+        rc = self._lib.nxs_create(device, max_records, finished_mask, C.byref(self._ctx))
+        if rc != _abi.NXS_OK:
+            self._ctx = None
+            raise NxsError(rc, f"nxs_create(device={device}, max_records={max_records})")
+        self.device = device
+        self.max_records = max_records
+        self.finished_mask = finished_mask
+        if stream is not None:
+            self.set_stream(stream)
+
+    def close(self):
+        if getattr(self, "_ctx", None):
+            self._lib.nxs_destroy(self._ctx)
+            self._ctx = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _check(self, rc):
+        if rc != _abi.NXS_OK:
+            raise NxsError(rc, self._lib.nxs_last_error(self._ctx).decode())
+
+    def set_stream(self, cuda_stream):
+        """cuda_stream: integer cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream)."""
+        self._check(self._lib.nxs_set_stream(self._ctx, C.c_void_p(int(cuda_stream))))
+
+    def sync(self):
+        self._check(self._lib.nxs_sync(self._ctx))
+
+    @property
+    def launches(self):
+        return int(self._lib.nxs_launch_count(self._ctx))
+
+    # ------------------------------------------------------------- host path
+    def classify(self, cols, out_verdict=None, out_rows=None):
+        """cols: dict of numpy arrays kind u8, reason_id u16, flags u8, cur_stage u8, job_key u64.
+        Returns (verdict u32[n], rows JOB_ROW[n_jobs])."""
+        kind = np.ascontiguousarray(cols["kind"], dtype=np.uint8)
+        reason = np.ascontiguousarray(cols["reason_id"], dtype=np.uint16)
+        flags = np.ascontiguousarray(cols["flags"], dtype=np.uint8)
+        stage = np.ascontiguousarray(cols["cur_stage"], dtype=np.uint8)
+        key = np.ascontiguousarray(cols["job_key"], dtype=np.uint64)
+        n = len(kind)
+        if not (len(reason) == len(flags) == len(stage) == len(key) == n):
+            raise ValueError("columns differ in length")
+        verdict = out_verdict if out_verdict is not None else np.empty(n, dtype=np.uint32)
+        rows = out_rows if out_rows is not None else np.empty(n, dtype=JOB_ROW)
+        n_jobs = C.c_uint64(0)
+        batch = _abi.Batch(kind.ctypes.data, reason.ctypes.data, flags.ctypes.data, stage.ctypes.data,
+                           key.ctypes.data, n)
+        out = _abi.Out(verdict.ctypes.data, rows.ctypes.data, C.addressof(n_jobs))
+        self._check(self._lib.nxs_classify(self._ctx, C.byref(batch), C.byref(out)))
+        return verdict[:n], rows[:n_jobs.value]
+
+    # ----------------------------------------------------------- device path
+    def classify_device(self, n, kind, reason_id, flags, cur_stage, job_key, verdict, job_rows, n_jobs):
+        """All arguments after n are device pointers (ints).  Asynchronous."""
+        batch = _abi.Batch(kind, reason_id, flags, cur_stage, job_key, n)
+        out = _abi.Out(verdict, job_rows, n_jobs)
+        self._check(self._lib.nxs_classify_device(self._ctx, C.byref(batch), C.byref(out)))
+
+    def generate_device(self, workload, n, kind, reason_id, flags, cur_stage, job_key, capacity,
+                        seed=DEFAULT_SEED, first=0, shard=0, n_shards=1):
+        """Fill device columns with a synthetic stream; returns the number of records written."""
+        cols = _abi.Columns(kind, reason_id, flags, cur_stage, job_key, capacity)
+        kept = C.c_uint64(0)
+        self._check(self._lib.nxs_generate_device(self._ctx, workload, seed, first, n, shard, n_shards,
+                                                  C.byref(cols), C.byref(kept)))
+        return int(kept.value)

@@ -1,0 +1,329 @@
+// nxs_classify.cu — context, launch logic and the C ABI declared in
+// include/nxs_classify.h.  The GPU path is the only path: no CPU fallback.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+#include "nxs_host.h"
+#include "nxs_kernel.cuh"
+
+using namespace nxs;
+
+struct nxs_ctx {
+  int device = 0;
+  int num_sms = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  uint64_t max_records = 0;
+  uint32_t finished_mask = 0;
+  uint32_t term_mask = 0;
+  int tile = 2048;        // records per tile (kernel variant)
+  int ctas_per_sm = 1;    // resident CTAs of the chosen variant
+  uint32_t max_tiles = 0;
+  TileDesc *desc = nullptr;
+  uint32_t *counters = nullptr;
+  uint32_t gen = 0;
+  uint64_t launches = 0;
+  uint8_t lut[128];
+  // staging for the host-pointer entry point (allocated on first use)
+  uint64_t staged_records = 0;
+  uint8_t *d_in = nullptr;
+  uint32_t *d_verdict = nullptr;
+  nxs_job_row *d_rows = nullptr;
+  uint64_t *d_njobs = nullptr;
+  uint64_t *h_njobs = nullptr; // pinned
+  char err[256] = {0};
+};
+
+namespace {
+
+int fail_cuda(nxs_ctx *ctx, cudaError_t e, const char *what) {
+  if (ctx) snprintf(ctx->err, sizeof ctx->err, "%s: %s", what, cudaGetErrorString(e));
+  return NXS_ERR_CUDA;
+}
+#define NXS_CUDA(ctx, call)                                 \
+  do {                                                      \
+    cudaError_t e_ = (call);                                \
+    if (e_ != cudaSuccess) return fail_cuda(ctx, e_, #call); \
+  } while (0)
+
+int fail_arg(nxs_ctx *ctx, const char *msg) {
+  if (ctx) snprintf(ctx->err, sizeof ctx->err, "%s", msg);
+  return NXS_ERR_ARG;
+}
+
+template <int TILE> int configure_variant(nxs_ctx *ctx) {
+  const size_t smem = classify_smem_bytes<TILE>();
+  NXS_CUDA(ctx, cudaFuncSetAttribute(classify_kernel<TILE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  NXS_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, classify_kernel<TILE>, kThreads, smem));
+  if (occ < 1) {
+    snprintf(ctx->err, sizeof ctx->err, "classify kernel does not fit on an SM");
+    return NXS_ERR_CUDA;
+  }
+  ctx->ctas_per_sm = occ;
+  return NXS_OK;
+}
+
+template <int TILE> int launch_variant(nxs_ctx *ctx, const ClassifyParams &p, uint32_t grid) {
+  classify_kernel<TILE><<<grid, kThreads, classify_smem_bytes<TILE>(), ctx->stream>>>(p);
+  NXS_CUDA(ctx, cudaGetLastError());
+  return NXS_OK;
+}
+
+bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+} // namespace
+
+extern "C" {
+
+int nxs_abi_version(void) { return NXS_ABI_VERSION; }
+
+const char *nxs_strerror(int status) {
+  switch (status) {
+  case NXS_OK: return "ok";
+  case NXS_ERR_ARG: return "invalid argument";
+  case NXS_ERR_CAPACITY: return "batch exceeds the context capacity";
+  case NXS_ERR_CUDA: return "CUDA error";
+  case NXS_ERR_NO_DEVICE: return "no CUDA device (this library has no CPU fallback)";
+  case NXS_ERR_NOMEM: return "out of memory";
+  case NXS_ERR_UNKNOWN_ACTION: return "unknown analysis result action";
+  default: return "unknown status";
+  }
+}
+
+const char *nxs_last_error(const nxs_ctx *ctx) { return ctx ? ctx->err : ""; }
+
+int nxs_create(int device, uint64_t max_records, uint16_t finished_mask, nxs_ctx **out) {
+  if (!out) return NXS_ERR_ARG;
+  *out = nullptr;
+  if (max_records == 0 || max_records >= 0xFFFFFFFFull) return NXS_ERR_CAPACITY;
+  int n_dev = 0;
+  if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0) {
+    cudaGetLastError();
+    return NXS_ERR_NO_DEVICE;
+  }
+  if (device < 0 || device >= n_dev) return NXS_ERR_ARG;
+  nxs_ctx *ctx = new (std::nothrow) nxs_ctx();
+  if (!ctx) return NXS_ERR_NOMEM;
+  ctx->device = device;
+  ctx->max_records = max_records;
+  ctx->finished_mask = finished_mask;
+  for (uint32_t a = 1; a <= 4; ++a)
+    if ((finished_mask >> new_stage_of(a)) & 1u) ctx->term_mask |= 1u << a;
+  nxs_build_lut(ctx->lut);
+  int rc = NXS_OK;
+  auto bail = [&](int code) {
+    nxs_destroy(ctx);
+    return code;
+  };
+  if (cudaSetDevice(device) != cudaSuccess) return bail(NXS_ERR_CUDA);
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return bail(NXS_ERR_CUDA);
+  if (prop.major < 10) return bail(NXS_ERR_NO_DEVICE); // sm_100a code only
+  ctx->num_sms = prop.multiProcessorCount;
+  const char *tile_env = getenv("NXS_TILE");
+  ctx->tile = tile_env ? atoi(tile_env) : 2048;
+  if (ctx->tile == 1024) rc = configure_variant<1024>(ctx);
+  else if (ctx->tile == 2048) rc = configure_variant<2048>(ctx);
+  else if (ctx->tile == 4096) rc = configure_variant<4096>(ctx);
+  else rc = NXS_ERR_ARG;
+  if (rc != NXS_OK) return bail(rc);
+  if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) return bail(NXS_ERR_CUDA);
+  ctx->own_stream = true;
+  ctx->max_tiles = (uint32_t)((max_records + ctx->tile - 1) / ctx->tile);
+  if (cudaMalloc(&ctx->desc, sizeof(TileDesc) * (size_t)ctx->max_tiles) != cudaSuccess) return bail(NXS_ERR_NOMEM);
+  if (cudaMalloc(&ctx->counters, 64) != cudaSuccess) return bail(NXS_ERR_NOMEM);
+  if (cudaMemset(ctx->desc, 0, sizeof(TileDesc) * (size_t)ctx->max_tiles) != cudaSuccess) return bail(NXS_ERR_CUDA);
+  if (cudaMemset(ctx->counters, 0, 64) != cudaSuccess) return bail(NXS_ERR_CUDA);
+  if (cudaMalloc(&ctx->d_njobs, 8) != cudaSuccess) return bail(NXS_ERR_NOMEM);
+  if (cudaMallocHost(&ctx->h_njobs, 8) != cudaSuccess) return bail(NXS_ERR_NOMEM);
+  *out = ctx;
+  return NXS_OK;
+}
+
+void nxs_destroy(nxs_ctx *ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream && ctx->own_stream) {
+    cudaStreamSynchronize(ctx->stream);
+    cudaStreamDestroy(ctx->stream);
+  }
+  cudaFree(ctx->desc);
+  cudaFree(ctx->counters);
+  cudaFree(ctx->d_in);
+  cudaFree(ctx->d_verdict);
+  cudaFree(ctx->d_rows);
+  cudaFree(ctx->d_njobs);
+  if (ctx->h_njobs) cudaFreeHost(ctx->h_njobs);
+  cudaGetLastError();
+  delete ctx;
+}
+
+int nxs_set_stream(nxs_ctx *ctx, void *cuda_stream) {
+  if (!ctx) return NXS_ERR_ARG;
+  if (ctx->own_stream && ctx->stream) {
+    cudaStreamSynchronize(ctx->stream);
+    cudaStreamDestroy(ctx->stream);
+  }
+  ctx->stream = static_cast<cudaStream_t>(cuda_stream);
+  ctx->own_stream = false;
+  return NXS_OK;
+}
+
+int nxs_sync(nxs_ctx *ctx) {
+  if (!ctx) return NXS_ERR_ARG;
+  NXS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return NXS_OK;
+}
+
+uint64_t nxs_launch_count(const nxs_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
+  if (!ctx || !in || !out) return NXS_ERR_ARG;
+  if (!out->n_jobs) return fail_arg(ctx, "out->n_jobs is null");
+  if (in->n > ctx->max_records) {
+    snprintf(ctx->err, sizeof ctx->err, "n=%llu exceeds max_records=%llu", (unsigned long long)in->n,
+             (unsigned long long)ctx->max_records);
+    return NXS_ERR_CAPACITY;
+  }
+  NXS_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (in->n == 0) {
+    NXS_CUDA(ctx, cudaMemsetAsync(out->n_jobs, 0, sizeof(uint64_t), ctx->stream));
+    return NXS_OK;
+  }
+  if (!in->kind || !in->reason_id || !in->flags || !in->cur_stage || !in->job_key || !out->verdict ||
+      !out->job_rows)
+    return fail_arg(ctx, "null column pointer");
+  if (!aligned16(in->kind) || !aligned16(in->reason_id) || !aligned16(in->flags) || !aligned16(in->cur_stage) ||
+      !aligned16(in->job_key) || !aligned16(out->job_rows) || (reinterpret_cast<uintptr_t>(out->verdict) & 3u))
+    return fail_arg(ctx, "device columns must be 16-byte aligned");
+
+  if (ctx->gen >= kGenMax) { // descriptor generation wrapped: start over from zeroed scratch
+    NXS_CUDA(ctx, cudaMemsetAsync(ctx->desc, 0, sizeof(TileDesc) * (size_t)ctx->max_tiles, ctx->stream));
+    ctx->gen = 0;
+  }
+  ClassifyParams p;
+  p.kind = in->kind;
+  p.reason = in->reason_id;
+  p.flags = in->flags;
+  p.stage = in->cur_stage;
+  p.key = in->job_key;
+  p.verdict = out->verdict;
+  p.rows = out->job_rows;
+  p.n_jobs = out->n_jobs;
+  p.desc = ctx->desc;
+  p.counters = ctx->counters;
+  p.n = (uint32_t)in->n;
+  p.n_tiles = (uint32_t)((in->n + ctx->tile - 1) / ctx->tile);
+  p.record_base = 0;
+  p.finished_mask = ctx->finished_mask;
+  p.term_mask = ctx->term_mask;
+  p.gen = ++ctx->gen;
+  memcpy(p.lut, ctx->lut, sizeof p.lut);
+  const uint32_t max_grid = (uint32_t)(ctx->num_sms * ctx->ctas_per_sm);
+  const uint32_t grid = p.n_tiles < max_grid ? p.n_tiles : max_grid;
+  uint32_t depth = p.n_tiles / grid;
+  p.depth = depth < 1 ? 1 : (depth > (uint32_t)kMaxStages ? (uint32_t)kMaxStages : depth);
+  int rc;
+  if (ctx->tile == 1024) rc = launch_variant<1024>(ctx, p, grid);
+  else if (ctx->tile == 2048) rc = launch_variant<2048>(ctx, p, grid);
+  else rc = launch_variant<4096>(ctx, p, grid);
+  if (rc == NXS_OK) ctx->launches += 1;
+  return rc;
+}
+
+static int ensure_staging(nxs_ctx *ctx, uint64_t n) {
+  if (n <= ctx->staged_records) return NXS_OK;
+  cudaFree(ctx->d_in);
+  cudaFree(ctx->d_verdict);
+  cudaFree(ctx->d_rows);
+  ctx->d_in = nullptr;
+  ctx->d_verdict = nullptr;
+  ctx->d_rows = nullptr;
+  ctx->staged_records = 0;
+  const uint64_t cap = (n + 1023) & ~1023ull; // keeps every column 16-byte aligned
+  if (cudaMalloc(&ctx->d_in, cap * 13) != cudaSuccess) return NXS_ERR_NOMEM;
+  if (cudaMalloc(&ctx->d_verdict, cap * 4) != cudaSuccess) return NXS_ERR_NOMEM;
+  if (cudaMalloc(&ctx->d_rows, cap * sizeof(nxs_job_row)) != cudaSuccess) return NXS_ERR_NOMEM;
+  ctx->staged_records = cap;
+  return NXS_OK;
+}
+
+int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
+  if (!ctx || !in || !out) return NXS_ERR_ARG;
+  if (!out->n_jobs) return fail_arg(ctx, "out->n_jobs is null");
+  if (in->n > ctx->max_records) return NXS_ERR_CAPACITY;
+  if (in->n == 0) {
+    *out->n_jobs = 0;
+    return NXS_OK;
+  }
+  if (!in->kind || !in->reason_id || !in->flags || !in->cur_stage || !in->job_key || !out->verdict ||
+      !out->job_rows)
+    return fail_arg(ctx, "null column pointer");
+  NXS_CUDA(ctx, cudaSetDevice(ctx->device));
+  int rc = ensure_staging(ctx, in->n);
+  if (rc != NXS_OK) {
+    cudaGetLastError();
+    snprintf(ctx->err, sizeof ctx->err, "cannot allocate device staging for %llu records",
+             (unsigned long long)in->n);
+    return rc;
+  }
+  const uint64_t n = in->n, cap = ctx->staged_records;
+  uint8_t *base = ctx->d_in;
+  uint64_t *d_key = reinterpret_cast<uint64_t *>(base);
+  uint16_t *d_reason = reinterpret_cast<uint16_t *>(base + cap * 8);
+  uint8_t *d_kind = base + cap * 10, *d_flags = base + cap * 11, *d_stage = base + cap * 12;
+  cudaStream_t st = ctx->stream;
+  NXS_CUDA(ctx, cudaMemcpyAsync(d_key, in->job_key, n * 8, cudaMemcpyHostToDevice, st));
+  NXS_CUDA(ctx, cudaMemcpyAsync(d_reason, in->reason_id, n * 2, cudaMemcpyHostToDevice, st));
+  NXS_CUDA(ctx, cudaMemcpyAsync(d_kind, in->kind, n, cudaMemcpyHostToDevice, st));
+  NXS_CUDA(ctx, cudaMemcpyAsync(d_flags, in->flags, n, cudaMemcpyHostToDevice, st));
+  NXS_CUDA(ctx, cudaMemcpyAsync(d_stage, in->cur_stage, n, cudaMemcpyHostToDevice, st));
+  nxs_batch d_in{d_kind, d_reason, d_flags, d_stage, d_key, n};
+  nxs_out d_out{ctx->d_verdict, ctx->d_rows, ctx->d_njobs};
+  rc = nxs_classify_device(ctx, &d_in, &d_out);
+  if (rc != NXS_OK) return rc;
+  NXS_CUDA(ctx, cudaMemcpyAsync(ctx->h_njobs, ctx->d_njobs, 8, cudaMemcpyDeviceToHost, st));
+  NXS_CUDA(ctx, cudaMemcpyAsync(out->verdict, ctx->d_verdict, n * 4, cudaMemcpyDeviceToHost, st));
+  NXS_CUDA(ctx, cudaStreamSynchronize(st));
+  const uint64_t n_jobs = *ctx->h_njobs;
+  if (n_jobs > n) {
+    snprintf(ctx->err, sizeof ctx->err, "internal error: n_jobs=%llu > n", (unsigned long long)n_jobs);
+    return NXS_ERR_CUDA;
+  }
+  NXS_CUDA(ctx, cudaMemcpyAsync(out->job_rows, ctx->d_rows, n_jobs * sizeof(nxs_job_row), cudaMemcpyDeviceToHost, st));
+  NXS_CUDA(ctx, cudaStreamSynchronize(st));
+  *out->n_jobs = n_jobs;
+  return NXS_OK;
+}
+
+int nxs_alloc_host(size_t bytes, void **out) {
+  if (!out) return NXS_ERR_ARG;
+  *out = nullptr;
+  if (cudaMallocHost(out, bytes ? bytes : 1) != cudaSuccess) {
+    cudaGetLastError();
+    return NXS_ERR_NOMEM;
+  }
+  return NXS_OK;
+}
+void nxs_free_host(void *p) {
+  if (p) cudaFreeHost(p);
+}
+
+} // extern "C"
+
+// Internal hooks for the other translation units of the library (not declared
+// in the public header).
+extern "C" int nxs_internal_ctx_info(nxs_ctx *ctx, int *device, void **stream, char **err, size_t *err_cap) {
+  if (!ctx) return NXS_ERR_ARG;
+  *device = ctx->device;
+  *stream = ctx->stream;
+  *err = ctx->err;
+  *err_cap = sizeof ctx->err;
+  return NXS_OK;
+}
+extern "C" void nxs_internal_count_launches(nxs_ctx *ctx, uint64_t n) {
+  if (ctx) ctx->launches += n;
+}

@@ -1,0 +1,234 @@
+// nxs_device.cuh — device-side building blocks of the classification kernel:
+// PTX wrappers (mbarrier, bulk async copy, acquire/release), the packed verdict
+// arithmetic and the per-job fold algebra.  sm_100a only.
+//
+// The fold algebra restates, as an associative operator over runs of records of
+// one job, what the reference does one event at a time in superviseAction
+// (services/supervisor.go:261-374): read the row, return if IsFinished(), else
+// apply the action's stage / cause / details.  See DESIGN.md "Per-job fold".
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "nxs_classify.h"
+
+namespace nxs {
+
+// ------------------------------------------------------------------ PTX glue
+#if defined(__CUDACC__)
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_n(uint64_t *bar, uint32_t n) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(n) : "memory");
+}
+// Arrival that fires once every cp.async this thread issued so far has landed.
+__device__ __forceinline__ void mbar_arrive_after_cp_async(uint64_t *bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ bool mbar_test_wait(uint64_t *bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+// 1-D bulk async copy global -> shared (TMA engine; SASS UBLKCP).  dst, src and
+// bytes are multiples of 16.
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_8(void *dst, const void *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ uint64_t ld_acquire(const uint64_t *p) {
+  uint64_t v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint64_t ld_relaxed(const uint64_t *p) {
+  uint64_t v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed(uint64_t *p, uint64_t v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void st_release(uint64_t *p, uint64_t v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t global_timer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+#endif // __CUDACC__
+
+// ------------------------------------------------------- verdict arithmetic
+// LUT entry ("code") for one (kind, reason): action | msg_tpl << 3; 0 = `default`.
+// applier switch (services/supervisor.go:283-370), indexed by action id
+__host__ __device__ __forceinline__ uint32_t new_stage_of(uint32_t action) {
+  // 1 -> SCHEDULING_FAILED(5) :297, 2 -> FAILED(4) :324, 3 -> DEADLINE_EXCEEDED(6) :349, 4 -> RUNNING(2) :362
+  return (0x26450u >> (action * 4)) & 15u;
+}
+__host__ __device__ __forceinline__ uint32_t cause_tpl_of(uint32_t action) {
+  // 1 -> T0 :298, 2 -> T1 :325, 3 -> message verbatim :350, 4 -> untouched :361-364
+  return (0xE4u >> (action * 2)) & 3u;
+}
+// Verdict of an APPLIED record with this action (msg_tpl added by the caller).
+__host__ __device__ __forceinline__ uint32_t applied_verdict(uint32_t action) {
+  return NXS_V_PACK(action, new_stage_of(action), cause_tpl_of(action), 0, action != NXS_ACTION_RUNNING, 1,
+                    0, 0);
+}
+
+// --------------------------------------------------------------- fold algebra
+// Summary of a run of consecutive records of ONE job, valid under the premise
+// "the row was not finished when the run began".  (If it was, nothing applies
+// and every handled record is a skip — resolve() handles that with s0.)
+struct Summ {
+  uint32_t win_idx; // record index of the winner (if F_HAS_WIN)
+  uint32_t f;
+};
+enum : uint32_t {
+  F_ANY_HE = 1u << 0,   // some record reached the switch-or-skip point (action != 0, checkpoint exists)
+  F_STOPPED = 1u << 1,  // an applied record moved the row to a finished stage
+  F_HAS_APP = 1u << 2,  // some record was applied
+  F_ALAST_SHIFT = 3,    // 3 bits: action of the last applied record
+  F_HAS_WIN = 1u << 6,  // some applied record had a failure action
+  F_CODEW_SHIFT = 7,    // 6 bits: LUT code (action | msg << 3) of the winner
+  F_SKIP = 1u << 13,    // some handled record came after the stop
+  F_ERR = 1u << 14,     // some record had no checkpoint
+  F_S0_SHIFT = 15,      // 4 bits: cur_stage of the job's first record
+  F_S0_VALID = 1u << 19,
+  F_ANCHORED = 1u << 20 // the run starts at the job's first record (look-back stops here)
+};
+constexpr uint32_t F_ALAST_MASK = 7u << F_ALAST_SHIFT;
+constexpr uint32_t F_CODEW_MASK = 63u << F_CODEW_SHIFT;
+constexpr uint32_t F_S0_MASK = 15u << F_S0_SHIFT;
+
+__host__ __device__ __forceinline__ Summ summ_identity() { return Summ{0u, 0u}; }
+__host__ __device__ __forceinline__ Summ summ_anchor(uint32_t s0) {
+  return Summ{0u, ((s0 & 15u) << F_S0_SHIFT) | F_S0_VALID | F_ANCHORED};
+}
+__host__ __device__ __forceinline__ uint64_t summ_pack(Summ s) {
+  return (uint64_t)s.f << 32 | s.win_idx;
+}
+__host__ __device__ __forceinline__ Summ summ_unpack(uint64_t v) {
+  return Summ{(uint32_t)v, (uint32_t)(v >> 32)};
+}
+
+// L then R (L earlier in record order).  Associative.
+__host__ __device__ __forceinline__ Summ summ_combine(Summ L, Summ R) {
+  uint32_t f = (L.f | R.f) & (F_ANY_HE | F_ERR | F_ANCHORED);
+  f |= ((L.f & F_S0_VALID) ? L.f : R.f) & (F_S0_MASK | F_S0_VALID);
+  uint32_t win;
+  if (L.f & F_STOPPED) {
+    f |= L.f & (F_STOPPED | F_HAS_APP | F_ALAST_MASK | F_HAS_WIN | F_CODEW_MASK | F_SKIP);
+    if (R.f & F_ANY_HE) f |= F_SKIP;
+    win = L.win_idx;
+  } else {
+    f |= R.f & F_STOPPED;
+    f |= (L.f | R.f) & (F_HAS_APP | F_SKIP);
+    f |= ((R.f & F_HAS_APP) ? R.f : L.f) & F_ALAST_MASK;
+    const bool rw = (R.f & F_HAS_WIN) != 0;
+    f |= (rw ? R.f : L.f) & (F_HAS_WIN | F_CODEW_MASK);
+    win = rw ? R.win_idx : L.win_idx;
+  }
+  return Summ{win, f};
+}
+
+// Summary of up to 32 consecutive records given as bit masks (bit b = record
+// base + b), already restricted to the run.  he: handled & checkpoint exists;
+// term: he & the action's stage is finished; fail: he & failure action; err:
+// handled & no checkpoint.  code[] holds the LUT code per record.
+__host__ __device__ __forceinline__ uint32_t hi_bit(uint32_t m) {
+#ifdef __CUDA_ARCH__
+  return 31u - __clz(m);
+#else
+  return 31u - __builtin_clz(m);
+#endif
+}
+__host__ __device__ __forceinline__ uint32_t lo_bit(uint32_t m) {
+#ifdef __CUDA_ARCH__
+  return __ffs(m) - 1u;
+#else
+  return __builtin_ctz(m);
+#endif
+}
+__host__ __device__ __forceinline__ Summ summ_piece(uint32_t he, uint32_t term, uint32_t fail, uint32_t err,
+                                                    const uint8_t *code, uint32_t base, uint32_t global_base) {
+  uint32_t f = err ? F_ERR : 0u;
+  uint32_t win = 0;
+  if (he) {
+    f |= F_ANY_HE | F_HAS_APP;
+    uint32_t app = he;
+    if (term) {
+      const uint32_t upto = (2u << lo_bit(term)) - 1u; // records up to and including the first stop
+      app = he & upto;
+      f |= F_STOPPED;
+      if (he & ~upto) f |= F_SKIP;
+    }
+    f |= (uint32_t)(code[base + hi_bit(app)] & 7u) << F_ALAST_SHIFT;
+    const uint32_t w = app & fail;
+    if (w) {
+      const uint32_t wp = hi_bit(w);
+      f |= F_HAS_WIN | (uint32_t)(code[base + wp] & 63u) << F_CODEW_SHIFT;
+      win = global_base + base + wp;
+    }
+  }
+  return Summ{win, f};
+}
+
+// Close a job: apply the premise check with s0 and emit (verdict, winner_idx).
+__host__ __device__ __forceinline__ void summ_resolve(Summ s, uint32_t finished_mask, uint32_t &verdict,
+                                                      uint32_t &winner) {
+  const uint32_t s0 = (s.f >> F_S0_SHIFT) & 15u;
+  const bool fin0 = (finished_mask >> s0) & 1u;
+  const bool any_he = (s.f & F_ANY_HE) != 0;
+  const bool err = (s.f & F_ERR) != 0;
+  const bool applied = !fin0 && (s.f & F_HAS_APP);
+  const bool skip = fin0 ? any_he : (s.f & F_SKIP) != 0;
+  const bool has_win = applied && (s.f & F_HAS_WIN);
+  const uint32_t a_last = applied ? (s.f >> F_ALAST_SHIFT) & 7u : 0u;
+  const uint32_t codew = (s.f >> F_CODEW_SHIFT) & 63u;
+  verdict = NXS_V_PACK(a_last, applied ? new_stage_of(a_last) : 0u, has_win ? cause_tpl_of(codew & 7u) : 0u,
+                       has_win ? codew >> 3 : 0u, (has_win || err) ? 1u : 0u, applied ? 1u : 0u,
+                       skip ? 1u : 0u, err ? NXS_ERR_NO_CHECKPOINT : 0u);
+  winner = has_win ? s.win_idx : NXS_NO_WINNER;
+}
+
+} // namespace nxs
