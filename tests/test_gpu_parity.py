@@ -1,0 +1,225 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU oracle — bit-exact.
+Run on the B200 box with `pytest -m gpu`."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import nexus_supervisor_b200 as nx
+from oracle import cpu_oracle
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "supervisor_test_scenarios.json")))
+STAGE_CONST = {"LifecycleStageSchedulingFailed": "SCHEDULING_FAILED", "LifecycleStageDeadlineExceeded":
+               "DEADLINE_EXCEEDED", "LifecycleStageRunning": "RUNNING", "LifecycleStageFailed": "FAILED",
+               "LifecycleStageCancelled": "CANCELLED"}
+
+
+@pytest.fixture(scope="module")
+def clf():
+    with nx.Classifier(device=0, max_records=1 << 23) as c:
+        yield c
+
+
+def test_golden_scenarios(clf):
+    """The 8 scenarios of services/supervisor_test.go, one batch, one record per job."""
+    sc = GOLDEN["scenarios"]
+    cols = util.make_cols([nx.KIND[s["kind"]] for s in sc], [nx.REASON[s["reason"]] for s in sc], [7] * len(sc),
+                          [nx.STAGE[s["seeded_stage"]] for s in sc], range(100, 100 + len(sc)))
+    verdict, rows = clf.classify(cols)
+    assert len(rows) == len(sc)
+    for s, v, row in zip(sc, verdict, rows):
+        f = nx.unpack_verdict(v)
+        final = f["new_stage"] if f["upsert"] else nx.STAGE[s["seeded_stage"]]
+        assert nx.stage_name(final) == STAGE_CONST[s["expected_stage_const"]], s
+        assert nx.unpack_verdict(row["verdict"])["new_stage"] == f["new_stage"]
+    util.assert_same(verdict, rows, *cpu_oracle.classify(cols), "golden")
+    # the OOMKilled scenario of BASELINE config 0: FAILED row, T1 + M2 cause, job deleted
+    g5 = nx.unpack_verdict(verdict[4])
+    assert (g5["new_stage"], g5["cause_tpl"], g5["msg_tpl"], g5["delete_job"]) == (nx.STAGE["FAILED"], 2, 3, 1)
+
+
+@pytest.mark.parametrize("fm", util.MASKS)
+def test_exhaustive_domain(fm):
+    with nx.Classifier(device=0, max_records=1 << 18, finished_mask=fm) as c:
+        for per_job in (1, 3):
+            cols = util.exhaustive_cols(per_job)
+            util.assert_same(*c.classify(cols), *cpu_oracle.classify(cols, fm), f"fm={fm:#x} per_job={per_job}")
+
+
+@pytest.mark.parametrize("n", [1, 2, 31, 32, 33, 2047, 2048, 2049, 4095, 4097, 6144, 100_003, 1_000_000])
+def test_ragged_sizes(clf, n):
+    rng = np.random.default_rng(n)
+    cols = util.random_cols(rng, n, 5)
+    util.assert_same(*clf.classify(cols), *cpu_oracle.classify(cols), f"n={n}")
+
+
+def test_empty_batch(clf):
+    verdict, rows = clf.classify(util.make_cols([], [], [], [], []))
+    assert len(verdict) == 0 and len(rows) == 0
+
+
+@pytest.mark.parametrize("max_len", [1, 2, 8, 40, 700, 5000, 400_000])
+def test_jobs_straddling_warps_tiles_and_ctas(clf, max_len):
+    """Jobs longer than a warp chunk, a tile and many tiles (look-back across head-less tiles)."""
+    rng = np.random.default_rng(max_len)
+    n = 700_001
+    for fm in (util.FM_DEFAULT, 0):
+        cols = util.random_cols(rng, n, max_len, wide=(fm == 0))
+        with nx.Classifier(device=0, max_records=n, finished_mask=fm) as c:
+            util.assert_same(*c.classify(cols), *cpu_oracle.classify(cols, fm), f"max_len={max_len} fm={fm:#x}")
+
+
+def test_single_job_batch(clf):
+    n = 300_000
+    rng = np.random.default_rng(3)
+    cols = util.random_cols(rng, n, 1, wide=False)
+    cols["job_key"][:] = 42
+    for fm in (util.FM_DEFAULT, 0):
+        with nx.Classifier(device=0, max_records=n, finished_mask=fm) as c:
+            verdict, rows = c.classify(cols)
+            assert len(rows) == 1
+            util.assert_same(verdict, rows, *cpu_oracle.classify(cols, fm), f"single job fm={fm:#x}")
+
+
+@pytest.mark.parametrize("tile", ["1024", "2048", "4096"])
+def test_tile_variants_and_context_reuse(tile, monkeypatch):
+    monkeypatch.setenv("NXS_TILE", tile)
+    rng = np.random.default_rng(int(tile))
+    with nx.Classifier(device=0, max_records=2_000_000) as c:
+        for n, max_len in ((1_500_000, 6), (5, 2), (777_777, 3000), (2_000_000, 2), (4096, 1)):
+            cols = util.random_cols(rng, n, max_len)
+            util.assert_same(*c.classify(cols), *cpu_oracle.classify(cols), f"tile={tile} n={n}")
+        assert c.launches == 5
+
+
+def test_errors_are_reported_not_thrown(clf):
+    with pytest.raises(nx.NxsError) as e:
+        clf.classify(util.random_cols(np.random.default_rng(0), (1 << 23) + 1, 2))
+    assert e.value.status == nx._abi.NXS_ERR_CAPACITY
+    with pytest.raises(nx.NxsError) as e:
+        nx.Classifier(device=99)
+    assert e.value.status == nx._abi.NXS_ERR_ARG
+    # misaligned device column
+    import torch
+    buf = torch.zeros(1 << 16, dtype=torch.uint8, device="cuda")
+    p = buf.data_ptr()
+    with pytest.raises(nx.NxsError) as e:
+        clf.classify_device(64, p + 1, p + 1024, p + 2048, p + 3072, p + 4096, p + 8192, p + 16384, p + 32768)
+    assert e.value.status == nx._abi.NXS_ERR_ARG
+
+
+# ----------------------------------------------------------------- device-resident path
+def _device_columns(torch, cap):
+    cap = (cap + 1023) & ~1023
+    raw = torch.empty(cap * 13, dtype=torch.uint8, device="cuda")
+    base = raw.data_ptr()
+    ptr = {"job_key": base, "reason_id": base + cap * 8, "kind": base + cap * 10, "flags": base + cap * 11,
+           "cur_stage": base + cap * 12}
+    return raw, ptr, cap
+
+
+def _fetch_columns(torch, raw, cap, n):
+    host = raw.cpu().numpy()
+    return {"job_key": host[:cap * 8].view(np.uint64)[:n].copy(),
+            "reason_id": host[cap * 8:cap * 10].view(np.uint16)[:n].copy(),
+            "kind": host[cap * 10:cap * 11][:n].copy(), "flags": host[cap * 11:cap * 12][:n].copy(),
+            "cur_stage": host[cap * 12:cap * 13][:n].copy()}
+
+
+@pytest.mark.parametrize("workload", [nx.WORKLOAD_UNIFORM, nx.WORKLOAD_SKEWED])
+def test_device_generator_matches_oracle_stream(clf, workload):
+    import torch
+    n = 1_000_000
+    raw, ptr, cap = _device_columns(torch, n)
+    clf.set_stream(torch.cuda.current_stream().cuda_stream)
+    kept = clf.generate_device(workload, n, ptr["kind"], ptr["reason_id"], ptr["flags"], ptr["cur_stage"],
+                               ptr["job_key"], cap, first=12345)
+    torch.cuda.synchronize()
+    assert kept == n
+    got = _fetch_columns(torch, raw, cap, n)
+    want = cpu_oracle.generate(workload, n, first=12345)
+    for k in want:
+        assert np.array_equal(got[k], want[k]), k
+
+
+def test_device_generator_shards(clf):
+    import torch
+    n = 600_000
+    raw, ptr, cap = _device_columns(torch, n)
+    clf.set_stream(torch.cuda.current_stream().cuda_stream)
+    total = 0
+    for shard in range(4):
+        kept = clf.generate_device(nx.WORKLOAD_SKEWED, n, ptr["kind"], ptr["reason_id"], ptr["flags"],
+                                   ptr["cur_stage"], ptr["job_key"], cap, shard=shard, n_shards=4)
+        torch.cuda.synchronize()
+        got = _fetch_columns(torch, raw, cap, kept)
+        want = cpu_oracle.generate(nx.WORKLOAD_SKEWED, n, shard=shard, n_shards=4)
+        assert kept == len(want["kind"])
+        for k in want:
+            assert np.array_equal(got[k], want[k]), (shard, k)
+        total += kept
+    assert total == n
+
+
+def _classify_device_full(torch, clf, ptr, n):
+    verdict = torch.empty(n, dtype=torch.int32, device="cuda")
+    rows = torch.empty((n, 2), dtype=torch.int64, device="cuda")
+    n_jobs = torch.zeros(1, dtype=torch.int64, device="cuda")
+    clf.classify_device(n, ptr["kind"], ptr["reason_id"], ptr["flags"], ptr["cur_stage"], ptr["job_key"],
+                        verdict.data_ptr(), rows.data_ptr(), n_jobs.data_ptr())
+    torch.cuda.synchronize()
+    return verdict, rows, int(n_jobs.item())
+
+
+def test_device_path_full_size_bit_exact():
+    """BASELINE config 2 at full size (1e8 skewed records, multi-record jobs), device-generated and
+    device-resident, compared bit for bit with the oracle in chunks cut on job boundaries; plus the
+    size-independent properties: job count == number of key changes, row keys == keys of each job's last
+    record, and a second launch reproduces the first."""
+    import torch
+    n = 100_000_000
+    with nx.Classifier(device=0, max_records=n) as clf:
+        clf.set_stream(torch.cuda.current_stream().cuda_stream)
+        raw, ptr, cap = _device_columns(torch, n)
+        kept = clf.generate_device(nx.WORKLOAD_SKEWED, n, ptr["kind"], ptr["reason_id"], ptr["flags"],
+                                   ptr["cur_stage"], ptr["job_key"], cap)
+        assert kept == n
+        verdict, rows, n_jobs = _classify_device_full(torch, clf, ptr, n)
+        keys = raw[:cap * 8].view(torch.int64)[:n]
+        tails = torch.ones(n, dtype=torch.bool, device="cuda")
+        tails[:-1] = keys[1:] != keys[:-1]
+        assert n_jobs == int(tails.sum().item())
+        assert torch.equal(rows[:n_jobs, 0], keys[tails])
+        del tails
+        verdict2, rows2, n_jobs2 = _classify_device_full(torch, clf, ptr, n)
+        assert n_jobs2 == n_jobs and torch.equal(verdict2, verdict) and torch.equal(rows2[:n_jobs], rows[:n_jobs])
+        del verdict2, rows2
+
+        threads = cpu_oracle.hardware_threads()
+        chunk = 10_000_000
+        lo, row_lo = 0, 0
+        while lo < n:
+            hi = min(n, lo + chunk)
+            want_cols = cpu_oracle.generate(nx.WORKLOAD_SKEWED, hi - lo + 64, first=lo)
+            if hi < n:  # extend to the end of the job that straddles the cut
+                k = want_cols["job_key"]
+                while k[hi - lo] == k[hi - lo - 1]:
+                    hi += 1
+            cols = {k: v[:hi - lo] for k, v in want_cols.items()}
+            got_keys = keys[lo:hi].cpu().numpy().view(np.uint64)
+            assert np.array_equal(got_keys, cols["job_key"]), f"generated keys differ in [{lo},{hi})"
+            want_v, want_r = cpu_oracle.classify(cols, threads=threads)
+            got_v = verdict[lo:hi].cpu().numpy().view(np.uint32)
+            got_r = rows[row_lo:row_lo + len(want_r)].cpu().numpy().view(np.uint64).reshape(-1, 2)
+            want_r = want_r.copy()
+            has_w = want_r["winner_idx"] != nx.NO_WINNER
+            want_r["winner_idx"][has_w] += np.uint32(lo)  # oracle indices are chunk-local
+            util.assert_same(got_v, got_r.copy().view(cpu_oracle.JOB_ROW).reshape(-1), want_v, want_r,
+                             f"records [{lo},{hi})")
+            row_lo += len(want_r)
+            lo = hi
+        assert row_lo == n_jobs

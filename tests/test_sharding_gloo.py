@@ -1,0 +1,77 @@
+"""World-size-2 test (gloo, CPU) of the multi-GPU host logic: shard by splitmix64(job_key) % G,
+classify each shard independently (here with the oracle — there is no GPU), gather on rank 0 and compare
+with one unsharded run.  No collective is involved in the data path itself; gloo only moves the
+per-shard results to rank 0, as the host-side gather would."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+from tests import util
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _worker(rank, world, port, n, seed, result_path):
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+    import nexus_supervisor_b200 as nx
+    from nexus_supervisor_b200 import sharding
+    from oracle import cpu_oracle
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rng = np.random.default_rng(seed)  # every rank builds the same stream
+    cols = util.random_cols(rng, n, 6)
+    shard_cols, idx = sharding.partition(cols, world)[rank]
+    # the scalar C-ABI function and the vectorised host function must agree
+    for k in shard_cols["job_key"][:50]:
+        assert nx.shard_of(int(k), world) == rank
+    v, rows = cpu_oracle.classify(shard_cols)
+    gathered = [None] * world if rank == 0 else None
+    dist.gather_object((v, rows, idx, shard_cols["job_key"]), gathered, dst=0)
+    if rank == 0:
+        got_v, got_r = sharding.gather(gathered, n)
+        want_v, want_r = cpu_oracle.classify(cols)
+        ok = np.array_equal(got_v, want_v) and np.array_equal(got_r, want_r)
+        np.save(result_path, np.array([int(ok), len(want_r), sum(len(g[2]) for g in gathered)]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2])
+def test_sharded_equals_unsharded(tmp_path, world):
+    import torch.multiprocessing as mp
+    n = 50_000
+    result = str(tmp_path / "result.npy")
+    mp.spawn(_worker, args=(world, _free_port(), n, 11, result), nprocs=world, join=True)
+    ok, n_rows, n_seen = np.load(result)
+    assert ok == 1 and n_seen == n and n_rows > 0
+
+
+def test_partition_keeps_jobs_whole_and_ordered():
+    from nexus_supervisor_b200 import sharding
+    from oracle import cpu_oracle
+    cols = cpu_oracle.generate(2, 100_000)
+    parts = sharding.partition(cols, 8)
+    assert sum(len(idx) for _, idx in parts) == 100_000
+    seen = set()
+    for s, (c, idx) in enumerate(parts):
+        assert (np.diff(idx) > 0).all()
+        keys = set(np.unique(c["job_key"]).tolist())
+        assert not (keys & seen)
+        seen |= keys
+        want = cpu_oracle.generate(2, 100_000, shard=s, n_shards=8)
+        for k in want:
+            assert np.array_equal(c[k], want[k])
+    sizes = np.array([len(idx) for _, idx in parts])
+    assert sizes.max() / sizes.mean() < 1.05

@@ -15,8 +15,14 @@ def make_cols(kind, reason, flags, stage, key):
 
 def random_cols(rng, n, max_job_len, wide=True):
     """Random records; jobs of 1..max_job_len adjacent records."""
-    lens = rng.integers(1, max_job_len + 1, size=n)
-    keys = np.repeat(np.arange(1, n + 1, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15), lens)[:n]
+    n_jobs = max(1, min(n, 4 * n // (max_job_len + 1) + 16))  # enough jobs to cover n records, bounded memory
+    lens = rng.integers(1, max_job_len + 1, size=n_jobs)
+    while int(lens.sum()) < n:
+        lens = np.concatenate([lens, rng.integers(1, max_job_len + 1, size=n_jobs)])
+    lens = lens[:int(np.searchsorted(np.cumsum(lens), n)) + 1]
+    with np.errstate(over="ignore"):
+        ids = np.arange(1, len(lens) + 1, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15)
+    keys = np.repeat(ids, lens)[:n]
     if wide:
         kind = rng.integers(0, 5, n)
         reason = rng.choice([0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 15, 31, 32, 500, 65535], n)
