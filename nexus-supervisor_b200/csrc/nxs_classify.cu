@@ -200,7 +200,7 @@ int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
       !aligned16(in->job_key) || !aligned16(out->job_rows) || (reinterpret_cast<uintptr_t>(out->verdict) & 3u))
     return fail_arg(ctx, "device columns must be 16-byte aligned");
 
-  if (ctx->gen >= kGenMax) { // descriptor generation wrapped: start over from zeroed scratch
+  if (ctx->gen >= kGenMax) { // 9-bit descriptor generation wrapped: start over from zeroed scratch
     NXS_CUDA(ctx, cudaMemsetAsync(ctx->desc, 0, sizeof(TileDesc) * (size_t)ctx->max_tiles, ctx->stream));
     ctx->gen = 0;
   }
@@ -224,8 +224,6 @@ int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
   memcpy(p.lut, ctx->lut, sizeof p.lut);
   const uint32_t max_grid = (uint32_t)(ctx->num_sms * ctx->ctas_per_sm);
   const uint32_t grid = p.n_tiles < max_grid ? p.n_tiles : max_grid;
-  uint32_t depth = p.n_tiles / grid;
-  p.depth = depth < 1 ? 1 : (depth > (uint32_t)kMaxStages ? (uint32_t)kMaxStages : depth);
   int rc;
   if (ctx->tile == 1024) rc = launch_variant<1024>(ctx, p, grid);
   else if (ctx->tile == 2048) rc = launch_variant<2048>(ctx, p, grid);
