@@ -40,7 +40,8 @@ typedef enum nxs_status {
   NXS_ERR_CUDA = -3,      /* a CUDA runtime call failed (see nxs_last_error) */
   NXS_ERR_NO_DEVICE = -4, /* no usable CUDA device: there is no CPU fallback */
   NXS_ERR_NOMEM = -5,
-  NXS_ERR_UNKNOWN_ACTION = -6 /* services/supervisor.go:371-372              */
+  NXS_ERR_UNKNOWN_ACTION = -6, /* services/supervisor.go:371-372             */
+  NXS_ERR_NOALLOC_LIMIT = -7   /* n > NXS_NOALLOC_MAX_RECORDS (static scratch) */
 } nxs_status;
 
 /* ------------------------------------------------- interned vocabularies */
@@ -192,6 +193,29 @@ int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *d_in,
                         const nxs_out *d_out);
 /* Number of kernels the ctx has launched so far (bench.py's gpu_launches). */
 uint64_t nxs_launch_count(const nxs_ctx *ctx);
+
+/* No counterpart in the reference.  The same classification as
+ * nxs_classify_device, for hosts that must not let a
+ * library allocate device memory — e.g. a service that gave its whole HBM budget
+ * to its own pool at start-up, so a cudaMalloc from here would fail or eat into
+ * it, or a latency-critical loop that cannot afford the device-wide stall a
+ * cudaMalloc/cudaFree can cause.  It needs no nxs_ctx and calls no allocating
+ * routine: the tile descriptors and counters the kernel uses as scratch live in
+ * a static __device__ array inside the library (about 128 KiB on every GPU that
+ * loads the library, until the process exits), which bounds a call to
+ * NXS_NOALLOC_MAX_RECORDS records; larger batches are refused with
+ * NXS_ERR_NOALLOC_LIMIT and nothing is launched.
+ *   - d_in / d_out hold DEVICE pointers with the same alignment rules as
+ *     nxs_classify_device; the work is asynchronous on `cuda_stream`.
+ *   - The first call on a device resolves the scratch array's device address and
+ *     configures the kernel for that device; make that first call before any
+ *     stream capture begins.
+ *   - All calls on a device share the one scratch array (each call clears the
+ *     part it uses first), so two calls whose GPU work can overlap — different
+ *     streams, or different threads — race; serialise them. */
+#define NXS_NOALLOC_MAX_RECORDS (1u << 24)
+int nxs_classify_device_noalloc(int device, void *cuda_stream, uint16_t finished_mask,
+                                const nxs_batch *d_in, const nxs_out *d_out);
 
 /* pinned host memory for nxs_classify callers */
 int nxs_alloc_host(size_t bytes, void **out);

@@ -12,6 +12,8 @@ LIB_PATH = os.path.join(_HERE, "lib", "libnxs_classify.so")
 NXS_OK = 0
 NXS_ERR_ARG, NXS_ERR_CAPACITY, NXS_ERR_CUDA, NXS_ERR_NO_DEVICE, NXS_ERR_NOMEM, NXS_ERR_UNKNOWN_ACTION = (
     -1, -2, -3, -4, -5, -6)
+NXS_ERR_NOALLOC_LIMIT = -7
+NXS_NOALLOC_MAX_RECORDS = 1 << 24
 
 u8p, u16p, u32p, u64p = (C.POINTER(t) for t in (C.c_uint8, C.c_uint16, C.c_uint32, C.c_uint64))
 
@@ -46,6 +48,7 @@ SIGNATURES = {
     "nxs_classify": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(Out)]),
     "nxs_classify_device": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(Out)]),
     "nxs_launch_count": (C.c_uint64, [C.c_void_p]),
+    "nxs_classify_device_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_uint16, C.POINTER(Batch), C.POINTER(Out)]),
     "nxs_alloc_host": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
     "nxs_free_host": (None, [C.c_void_p]),
     "nxs_intern_kind": (C.c_uint8, [C.c_char_p, C.c_size_t]),

@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 
 #include "nxs_host.h"
@@ -89,6 +90,7 @@ const char *nxs_strerror(int status) {
   case NXS_ERR_NO_DEVICE: return "no CUDA device (this library has no CPU fallback)";
   case NXS_ERR_NOMEM: return "out of memory";
   case NXS_ERR_UNKNOWN_ACTION: return "unknown analysis result action";
+  case NXS_ERR_NOALLOC_LIMIT: return "batch exceeds NXS_NOALLOC_MAX_RECORDS (the static scratch of the no-alloc entry point)";
   default: return "unknown status";
   }
 }
@@ -311,6 +313,115 @@ void nxs_free_host(void *p) {
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------------------
+// Allocation-free entry point.
+//
+// For callers that cannot let this library allocate device memory (their own
+// pool owns the HBM budget, or a cudaMalloc/cudaFree stall is unacceptable on
+// their hot loop).  The kernel's scratch — one 16-byte descriptor per tile plus
+// the counters — lives in this file-scope __device__ array instead of a
+// cudaMalloc'ed buffer: 2048-record tiles, so NXS_NOALLOC_MAX_RECORDS = 2^24
+// records need 8192 descriptors (128 KiB) + 256 bytes for the counters.  Every
+// GPU that loads the library carries the array until the process exits.
+//
+// `g_noalloc_scratch` as written in host code is only a host-side handle for the
+// symbol, never a device address: the address each device gave the array is
+// looked up once per device with cudaGetSymbolAddress and handed to the kernel.
+constexpr int kNoallocTile = 2048;
+constexpr uint32_t kNoallocMaxTiles = NXS_NOALLOC_MAX_RECORDS / kNoallocTile;
+constexpr size_t kNoallocCounterBytes = 256;
+constexpr size_t kNoallocScratchBytes = kNoallocCounterBytes + sizeof(TileDesc) * kNoallocMaxTiles;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoallocScratchBytes];
+
+namespace {
+constexpr int kNoallocMaxDevices = 64;
+struct NoallocDevice {
+  bool ready = false;
+  unsigned char *scratch = nullptr; // device address of g_noalloc_scratch on this device
+  uint32_t max_grid = 0;
+};
+NoallocDevice g_noalloc_dev[kNoallocMaxDevices];
+std::mutex g_noalloc_mutex;
+
+// Once per device, with that device current.
+int noalloc_setup(int device, NoallocDevice **out) {
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  NoallocDevice &d = g_noalloc_dev[device];
+  if (!d.ready) {
+    void *addr = nullptr;
+    if (cudaGetSymbolAddress(&addr, g_noalloc_scratch) != cudaSuccess || addr == nullptr) {
+      cudaGetLastError();
+      return NXS_ERR_CUDA;
+    }
+    const size_t smem = classify_smem_bytes<kNoallocTile>();
+    int sms = 0, occ = 0;
+    if (cudaFuncSetAttribute(classify_kernel<kNoallocTile>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, classify_kernel<kNoallocTile>, kThreads, smem) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || occ < 1 || sms < 1) {
+      cudaGetLastError();
+      return NXS_ERR_CUDA;
+    }
+    d.scratch = static_cast<unsigned char *>(addr);
+    d.max_grid = (uint32_t)(sms * occ);
+    d.ready = true;
+  }
+  *out = &d;
+  return NXS_OK;
+}
+} // namespace
+
+extern "C" int nxs_classify_device_noalloc(int device, void *cuda_stream, uint16_t finished_mask,
+                                           const nxs_batch *in, const nxs_out *out) {
+  if (!in || !out || !out->n_jobs) return NXS_ERR_ARG;
+  if (in->n > NXS_NOALLOC_MAX_RECORDS) return NXS_ERR_NOALLOC_LIMIT; // refused before anything is touched
+  if (device < 0 || device >= kNoallocMaxDevices) return NXS_ERR_ARG;
+  if (cudaSetDevice(device) != cudaSuccess) {
+    cudaGetLastError();
+    return NXS_ERR_ARG;
+  }
+  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  if (in->n == 0) return cudaMemsetAsync(out->n_jobs, 0, sizeof(uint64_t), stream) == cudaSuccess ? NXS_OK : NXS_ERR_CUDA;
+  if (!in->kind || !in->reason_id || !in->flags || !in->cur_stage || !in->job_key || !out->verdict || !out->job_rows)
+    return NXS_ERR_ARG;
+  if (!aligned16(in->kind) || !aligned16(in->reason_id) || !aligned16(in->flags) || !aligned16(in->cur_stage) ||
+      !aligned16(in->job_key) || !aligned16(out->job_rows) || (reinterpret_cast<uintptr_t>(out->verdict) & 3u))
+    return NXS_ERR_ARG;
+  NoallocDevice *dev = nullptr;
+  int rc = noalloc_setup(device, &dev);
+  if (rc != NXS_OK) return rc;
+
+  ClassifyParams p;
+  p.kind = in->kind;
+  p.reason = in->reason_id;
+  p.flags = in->flags;
+  p.stage = in->cur_stage;
+  p.key = in->job_key;
+  p.verdict = out->verdict;
+  p.rows = out->job_rows;
+  p.n_jobs = out->n_jobs;
+  p.counters = reinterpret_cast<uint32_t *>(dev->scratch);
+  p.desc = reinterpret_cast<TileDesc *>(dev->scratch + kNoallocCounterBytes);
+  p.n = (uint32_t)in->n;
+  p.n_tiles = (uint32_t)((in->n + kNoallocTile - 1) / kNoallocTile);
+  p.record_base = 0;
+  p.finished_mask = finished_mask;
+  p.term_mask = 0;
+  for (uint32_t a = 1; a <= 4; ++a)
+    if ((finished_mask >> new_stage_of(a)) & 1u) p.term_mask |= 1u << a;
+  p.gen = 1;
+  nxs_build_lut(p.lut);
+  // The array still holds the previous call's descriptors and counters: the counters and every
+  // descriptor this launch will read must start at zero.
+  if (cudaMemsetAsync(dev->scratch, 0, kNoallocCounterBytes + sizeof(TileDesc) * (size_t)p.n_tiles, stream) != cudaSuccess) {
+    cudaGetLastError();
+    return NXS_ERR_CUDA;
+  }
+  const uint32_t grid = p.n_tiles < dev->max_grid ? p.n_tiles : dev->max_grid;
+  classify_kernel<kNoallocTile><<<grid, kThreads, classify_smem_bytes<kNoallocTile>(), stream>>>(p);
+  if (cudaGetLastError() != cudaSuccess) return NXS_ERR_CUDA;
+  return NXS_OK;
+}
 
 // Internal hooks for the other translation units of the library (not declared
 // in the public header).
