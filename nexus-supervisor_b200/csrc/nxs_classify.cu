@@ -35,6 +35,9 @@ struct nxs_ctx {
   uint64_t *d_njobs = nullptr;
   uint64_t *h_njobs = nullptr; // pinned
   char err[256] = {0};
+#ifdef NXS_TRACE
+  unsigned long long *trace = nullptr;
+#endif
 };
 
 namespace {
@@ -202,7 +205,7 @@ int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
       !aligned16(in->job_key) || !aligned16(out->job_rows) || (reinterpret_cast<uintptr_t>(out->verdict) & 3u))
     return fail_arg(ctx, "device columns must be 16-byte aligned");
 
-  if (ctx->gen >= kGenMax) { // 9-bit descriptor generation wrapped: start over from zeroed scratch
+  if (ctx->gen >= kGenMax) { // 7-bit descriptor generation wrapped: start over from zeroed scratch
     NXS_CUDA(ctx, cudaMemsetAsync(ctx->desc, 0, sizeof(TileDesc) * (size_t)ctx->max_tiles, ctx->stream));
     ctx->gen = 0;
   }
@@ -224,6 +227,12 @@ int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
   p.term_mask = ctx->term_mask;
   p.gen = ++ctx->gen;
   memcpy(p.lut, ctx->lut, sizeof p.lut);
+#ifdef NXS_TRACE
+  if (!ctx->trace) cudaMalloc(&ctx->trace, 8 + 16 * (size_t)(1 << 20));
+  cudaMemsetAsync(ctx->trace, 0, 8, ctx->stream);
+  p.trace = ctx->trace;
+  p.trace_cap = 1 << 20;
+#endif
   const uint32_t max_grid = (uint32_t)(ctx->num_sms * ctx->ctas_per_sm);
   const uint32_t grid = p.n_tiles < max_grid ? p.n_tiles : max_grid;
   int rc;
@@ -410,6 +419,10 @@ extern "C" int nxs_classify_device_noalloc(int device, void *cuda_stream, uint16
   for (uint32_t a = 1; a <= 4; ++a)
     if ((finished_mask >> new_stage_of(a)) & 1u) p.term_mask |= 1u << a;
   p.gen = 1;
+#ifdef NXS_TRACE
+  p.trace = nullptr;
+  p.trace_cap = 0;
+#endif
   nxs_build_lut(p.lut);
   // The array still holds the previous call's descriptors and counters: the counters and every
   // descriptor this launch will read must start at zero.
@@ -422,6 +435,20 @@ extern "C" int nxs_classify_device_noalloc(int device, void *cuda_stream, uint16
   if (cudaGetLastError() != cudaSuccess) return NXS_ERR_CUDA;
   return NXS_OK;
 }
+
+#ifdef NXS_TRACE
+// Debug build only: copies the event log of the last launch to the host.  Returns the event count.
+extern "C" long long nxs_debug_dump_trace(nxs_ctx *ctx, unsigned long long *host, unsigned long long max_events) {
+  if (!ctx || !ctx->trace) return -1;
+  cudaStreamSynchronize(ctx->stream);
+  unsigned long long n = 0;
+  cudaMemcpy(&n, ctx->trace, 8, cudaMemcpyDeviceToHost);
+  if (n > (1ull << 20)) n = 1ull << 20;
+  if (n > max_events) n = max_events;
+  cudaMemcpy(host, ctx->trace + 1, n * 16, cudaMemcpyDeviceToHost);
+  return (long long)n;
+}
+#endif
 
 // Internal hooks for the other translation units of the library (not declared
 // in the public header).

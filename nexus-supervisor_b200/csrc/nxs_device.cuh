@@ -37,16 +37,29 @@ __device__ __forceinline__ void mbar_arrive_n(uint64_t *bar, uint32_t n) {
 __device__ __forceinline__ void mbar_arrive_after_cp_async(uint64_t *bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
+// Suspends the thread until the phase completes or about `hint_ns` have passed.
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity, uint32_t hint_ns = 20000u) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
       "selp.u32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(hint_ns)
       : "memory");
   return ok != 0;
+}
+// Warp ballot of one bit of a word (one LOP3 + one VOTE).
+__device__ __forceinline__ uint32_t ballot_bit(uint32_t word, uint32_t bit) {
+  uint32_t r;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b32 t;\n\t"
+      "and.b32 t, %1, %2;\n\t"
+      "setp.ne.u32 p, t, 0;\n\t"
+      "vote.sync.ballot.b32 %0, p, 0xffffffff;\n\t}"
+      : "=r"(r)
+      : "r"(word), "r"(bit));
+  return r;
 }
 __device__ __forceinline__ bool mbar_test_wait(uint64_t *bar, uint32_t parity) {
   uint32_t ok;
@@ -99,7 +112,8 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
 #endif // __CUDACC__
 
 // ------------------------------------------------------- verdict arithmetic
-// LUT entry ("code") for one (kind, reason): action | msg_tpl << 3; 0 = `default`.
+// LUT entry ("code") for one (kind, reason): action | cause_tpl << 3 | msg_tpl << 5;
+// 0 = `default`.
 // applier switch (services/supervisor.go:283-370), indexed by action id
 __host__ __device__ __forceinline__ uint32_t new_stage_of(uint32_t action) {
   // 1 -> SCHEDULING_FAILED(5) :297, 2 -> FAILED(4) :324, 3 -> DEADLINE_EXCEEDED(6) :349, 4 -> RUNNING(2) :362
@@ -108,6 +122,9 @@ __host__ __device__ __forceinline__ uint32_t new_stage_of(uint32_t action) {
 __host__ __device__ __forceinline__ uint32_t cause_tpl_of(uint32_t action) {
   // 1 -> T0 :298, 2 -> T1 :325, 3 -> message verbatim :350, 4 -> untouched :361-364
   return (0xE4u >> (action * 2)) & 3u;
+}
+__host__ __device__ __forceinline__ uint32_t make_code(uint32_t action, uint32_t msg_tpl) {
+  return action | cause_tpl_of(action) << 3 | msg_tpl << 5;
 }
 // Verdict of an APPLIED record with this action (msg_tpl added by the caller).
 __host__ __device__ __forceinline__ uint32_t applied_verdict(uint32_t action) {
@@ -118,31 +135,32 @@ __host__ __device__ __forceinline__ uint32_t applied_verdict(uint32_t action) {
 // --------------------------------------------------------------- fold algebra
 // Summary of a run of consecutive records of ONE job, valid under the premise
 // "the row was not finished when the run began".  (If it was, nothing applies
-// and every handled record is a skip — resolve() handles that with s0.)
+// and every handled record is a skip — summ_resolve handles that with s0.)
+// The low 16 bits sit where the packed verdict has the same fields, so closing a
+// job is mostly a mask.
 struct Summ {
   uint32_t win_idx; // record index of the winner (if F_HAS_WIN)
   uint32_t f;
 };
 enum : uint32_t {
-  F_ANY_HE = 1u << 0,   // some record reached the switch-or-skip point (action != 0, checkpoint exists)
-  F_STOPPED = 1u << 1,  // an applied record moved the row to a finished stage
-  F_HAS_APP = 1u << 2,  // some record was applied
-  F_ALAST_SHIFT = 3,    // 3 bits: action of the last applied record
-  F_HAS_WIN = 1u << 6,  // some applied record had a failure action
-  F_CODEW_SHIFT = 7,    // 6 bits: LUT code (action | msg << 3) of the winner
-  F_SKIP = 1u << 13,    // some handled record came after the stop
-  F_ERR = 1u << 14,     // some record had no checkpoint
-  F_S0_SHIFT = 15,      // 4 bits: cur_stage of the job's first record
-  F_S0_VALID = 1u << 19,
-  F_ANCHORED = 1u << 20 // the run starts at the job's first record (look-back stops here)
+  F_ALAST_MASK = 7u,      // bits 0-2: action of the last applied record (verdict.action)
+  F_WIN_SHIFT = 7,        // bits 7-8 cause_tpl, bits 9-11 msg_tpl of the winner (verdict.cause_tpl/msg_tpl)
+  F_WIN_MASK = 31u << 7,
+  F_HAS_WIN = 1u << 12,   // some applied record had a failure action (verdict.delete_job)
+  F_HAS_APP = 1u << 13,   // some handled record with a checkpoint: applied under the premise (verdict.upsert)
+  F_SKIP = 1u << 14,      // some handled record came after the stop (verdict.skip_finished)
+  F_ERR = 1u << 15,       // some record had no checkpoint (verdict.err = 1)
+  F_STOPPED = 1u << 17,   // an applied record moved the row to a finished stage
+  F_S0_SHIFT = 18,        // bits 18-21: cur_stage of the job's first record (valid iff anchored)
+  F_S0_MASK = 15u << 18,
+  F_ANCHORED = 1u << 22,  // the run starts at the job's first record (look-back stops here)
+  F_BITS = 23
 };
-constexpr uint32_t F_ALAST_MASK = 7u << F_ALAST_SHIFT;
-constexpr uint32_t F_CODEW_MASK = 63u << F_CODEW_SHIFT;
-constexpr uint32_t F_S0_MASK = 15u << F_S0_SHIFT;
+constexpr uint32_t F_VERDICT_MASK = F_ALAST_MASK | F_WIN_MASK | F_HAS_WIN | F_HAS_APP | F_SKIP | F_ERR;
 
 __host__ __device__ __forceinline__ Summ summ_identity() { return Summ{0u, 0u}; }
 __host__ __device__ __forceinline__ Summ summ_anchor(uint32_t s0) {
-  return Summ{0u, ((s0 & 15u) << F_S0_SHIFT) | F_S0_VALID | F_ANCHORED};
+  return Summ{0u, ((s0 & 15u) << F_S0_SHIFT) | F_ANCHORED};
 }
 __host__ __device__ __forceinline__ uint64_t summ_pack(Summ s) {
   return (uint64_t)s.f << 32 | s.win_idx;
@@ -153,64 +171,78 @@ __host__ __device__ __forceinline__ Summ summ_unpack(uint64_t v) {
 
 // L then R (L earlier in record order).  Associative.
 __host__ __device__ __forceinline__ Summ summ_combine(Summ L, Summ R) {
-  uint32_t f = (L.f | R.f) & (F_ANY_HE | F_ERR | F_ANCHORED);
-  f |= ((L.f & F_S0_VALID) ? L.f : R.f) & (F_S0_MASK | F_S0_VALID);
+  uint32_t f = (L.f | R.f) & F_ERR;
+  f |= ((L.f & F_ANCHORED) ? L.f : R.f) & (F_S0_MASK | F_ANCHORED);
   uint32_t win;
   if (L.f & F_STOPPED) {
-    f |= L.f & (F_STOPPED | F_HAS_APP | F_ALAST_MASK | F_HAS_WIN | F_CODEW_MASK | F_SKIP);
-    if (R.f & F_ANY_HE) f |= F_SKIP;
+    f |= L.f & (F_STOPPED | F_HAS_APP | F_ALAST_MASK | F_HAS_WIN | F_WIN_MASK | F_SKIP);
+    if (R.f & F_HAS_APP) f |= F_SKIP;
     win = L.win_idx;
   } else {
     f |= R.f & F_STOPPED;
     f |= (L.f | R.f) & (F_HAS_APP | F_SKIP);
     f |= ((R.f & F_HAS_APP) ? R.f : L.f) & F_ALAST_MASK;
     const bool rw = (R.f & F_HAS_WIN) != 0;
-    f |= (rw ? R.f : L.f) & (F_HAS_WIN | F_CODEW_MASK);
+    f |= (rw ? R.f : L.f) & (F_HAS_WIN | F_WIN_MASK);
     win = rw ? R.win_idx : L.win_idx;
   }
   return Summ{win, f};
 }
 
-// Summary of up to 32 consecutive records given as bit masks (bit b = record
-// base + b), already restricted to the run.  he: handled & checkpoint exists;
-// term: he & the action's stage is finished; fail: he & failure action; err:
-// handled & no checkpoint.  code[] holds the LUT code per record.
-__host__ __device__ __forceinline__ uint32_t hi_bit(uint32_t m) {
+__host__ __device__ __forceinline__ uint32_t hi_bit(uint32_t m) { // m != 0
 #ifdef __CUDA_ARCH__
-  return 31u - __clz(m);
+  uint32_t r;
+  asm("bfind.u32 %0, %1;" : "=r"(r) : "r"(m));
+  return r;
 #else
   return 31u - __builtin_clz(m);
 #endif
 }
-__host__ __device__ __forceinline__ uint32_t lo_bit(uint32_t m) {
+__host__ __device__ __forceinline__ uint32_t lo_bit(uint32_t m) { // m != 0
 #ifdef __CUDA_ARCH__
   return __ffs(m) - 1u;
 #else
   return __builtin_ctz(m);
 #endif
 }
+
+// Flag part of the summary of up to 32 consecutive records given as bit masks
+// (bit b = record b of the chunk), already restricted to the run.  he: handled &
+// checkpoint exists; term: he & the action's stage is finished; fail: he &
+// failure action; err: handled & no checkpoint.  Returns the flags without the
+// winner's code; win_pos = chunk position of the winner (meaningful iff F_HAS_WIN),
+// last_is_win = the last applied record is the winner (else it is a ToRunning).
+__host__ __device__ __forceinline__ uint32_t summ_piece_flags(uint32_t he, uint32_t term, uint32_t fail,
+                                                              uint32_t err, uint32_t &win_pos, bool &last_is_win) {
+  uint32_t f = err ? F_ERR : 0u;
+  uint32_t app = he;
+  if (term) {
+    const uint32_t upto = (2u << lo_bit(term)) - 1u; // records up to and including the first stop
+    app = he & upto;
+    f |= F_STOPPED;
+    if (he & ~upto) f |= F_SKIP;
+  }
+  if (he) f |= F_HAS_APP;
+  const uint32_t wm = app & fail;
+  win_pos = hi_bit(wm | 1u);
+  last_is_win = wm != 0 && win_pos == hi_bit(app | 1u);
+  if (wm) f |= F_HAS_WIN;
+  return f;
+}
+// Completes the flags with the winner's LUT code.
+__host__ __device__ __forceinline__ uint32_t summ_piece_finish(uint32_t f, uint32_t code_w, bool last_is_win) {
+  if (f & F_HAS_WIN) f |= (code_w >> 3) << F_WIN_SHIFT;
+  if (f & F_HAS_APP) f |= last_is_win ? (code_w & 7u) : (uint32_t)NXS_ACTION_RUNNING;
+  return f;
+}
+// Convenience form with the codes in memory (host walk-through, long-job paths).
 __host__ __device__ __forceinline__ Summ summ_piece(uint32_t he, uint32_t term, uint32_t fail, uint32_t err,
                                                     const uint8_t *code, uint32_t base, uint32_t global_base) {
-  uint32_t f = err ? F_ERR : 0u;
-  uint32_t win = 0;
-  if (he) {
-    f |= F_ANY_HE | F_HAS_APP;
-    uint32_t app = he;
-    if (term) {
-      const uint32_t upto = (2u << lo_bit(term)) - 1u; // records up to and including the first stop
-      app = he & upto;
-      f |= F_STOPPED;
-      if (he & ~upto) f |= F_SKIP;
-    }
-    f |= (uint32_t)(code[base + hi_bit(app)] & 7u) << F_ALAST_SHIFT;
-    const uint32_t w = app & fail;
-    if (w) {
-      const uint32_t wp = hi_bit(w);
-      f |= F_HAS_WIN | (uint32_t)(code[base + wp] & 63u) << F_CODEW_SHIFT;
-      win = global_base + base + wp;
-    }
-  }
-  return Summ{win, f};
+  uint32_t wp;
+  bool liw;
+  const uint32_t f = summ_piece_flags(he, term, fail, err, wp, liw);
+  const uint32_t cw = (f & F_HAS_WIN) ? code[base + wp] : 0u;
+  return Summ{(f & F_HAS_WIN) ? global_base + base + wp : 0u, summ_piece_finish(f, cw, liw)};
 }
 
 // Close a job: apply the premise check with s0 and emit (verdict, winner_idx).
@@ -218,17 +250,11 @@ __host__ __device__ __forceinline__ void summ_resolve(Summ s, uint32_t finished_
                                                       uint32_t &winner) {
   const uint32_t s0 = (s.f >> F_S0_SHIFT) & 15u;
   const bool fin0 = (finished_mask >> s0) & 1u;
-  const bool any_he = (s.f & F_ANY_HE) != 0;
-  const bool err = (s.f & F_ERR) != 0;
-  const bool applied = !fin0 && (s.f & F_HAS_APP);
-  const bool skip = fin0 ? any_he : (s.f & F_SKIP) != 0;
-  const bool has_win = applied && (s.f & F_HAS_WIN);
-  const uint32_t a_last = applied ? (s.f >> F_ALAST_SHIFT) & 7u : 0u;
-  const uint32_t codew = (s.f >> F_CODEW_SHIFT) & 63u;
-  verdict = NXS_V_PACK(a_last, applied ? new_stage_of(a_last) : 0u, has_win ? cause_tpl_of(codew & 7u) : 0u,
-                       has_win ? codew >> 3 : 0u, (has_win || err) ? 1u : 0u, applied ? 1u : 0u,
-                       skip ? 1u : 0u, err ? NXS_ERR_NO_CHECKPOINT : 0u);
-  winner = has_win ? s.win_idx : NXS_NO_WINNER;
+  uint32_t v;
+  if (fin0) v = ((s.f & F_HAS_APP) ? F_SKIP : 0u) | (s.f & F_ERR);
+  else v = (s.f & F_VERDICT_MASK) | new_stage_of(s.f & F_ALAST_MASK) << 3;
+  verdict = v | (s.f & F_ERR) >> 3; // a missing checkpoint also deletes the job (:268)
+  winner = (!fin0 && (s.f & F_HAS_WIN)) ? s.win_idx : NXS_NO_WINNER;
 }
 
 } // namespace nxs

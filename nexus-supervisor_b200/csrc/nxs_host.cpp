@@ -75,7 +75,10 @@ bool eq(const char *s, size_t len, const char *lit) { return strlen(lit) == len 
 namespace nxs {
 void nxs_build_lut(uint8_t lut[128]) {
   memset(lut, 0, 128);
-  for (const SwitchArm &a : kSwitchArms) lut[a.kind * 32 + a.reason] = (uint8_t)(a.action | a.msg_tpl << 3);
+  // code = action | cause_tpl << 3 | msg_tpl << 5; cause template per action: :298, :325, :350, none for ToRunning
+  static const uint8_t cause_of_action[5] = {0, 1, 2, 3, 0};
+  for (const SwitchArm &a : kSwitchArms)
+    lut[a.kind * 32 + a.reason] = (uint8_t)(a.action | cause_of_action[a.action] << 3 | a.msg_tpl << 5);
 }
 } // namespace nxs
 

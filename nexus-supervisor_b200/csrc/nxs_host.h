@@ -7,7 +7,7 @@
 namespace nxs {
 // Fills the 128-entry (kind, reason) -> code table the kernel stages in shared
 // memory: index = min(kind,3)*32 + (reason < 32 ? reason : 0),
-// code = action | msg_tpl << 3, 0 for every `default` arm.
+// code = action | cause_tpl << 3 | msg_tpl << 5, 0 for every `default` arm.
 void nxs_build_lut(uint8_t lut[128]);
 inline uint64_t splitmix64(uint64_t x) {
   uint64_t z = x + 0x9E3779B97F4A7C15ull;

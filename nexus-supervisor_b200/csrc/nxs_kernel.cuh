@@ -8,11 +8,18 @@
 //   producer warp  claims tile ids from a global counter and streams the five
 //                  input columns of a tile into a stage with 1-D bulk async
 //                  copies (TMA engine, SASS UBLKCP)
-//   worker warps   phase 1 as soon as a tile has landed: lane-per-record LUT
-//                  lookup, guards, packed verdict -> global; warp ballots ->
-//                  per-32-record bit masks in shared memory
-//                  phase 2 once the tile's look-back is done: lanes holding the
-//                  LAST record of a job resolve its masks into the 16-byte row
+//   worker warps   phase 1 as soon as a tile has landed.  Each warp owns a
+//                  contiguous range of the tile (TILE/8 records) and walks it 32
+//                  records at a time, lane per record: table lookups -> packed
+//                  verdict -> global; warp ballots -> bit masks kept in
+//                  registers; the lane holding the LAST record of a job folds the
+//                  job's masks into its row right away (codes of other lanes come
+//                  by shuffle, the job left open by the previous 32 records is
+//                  carried in registers) and parks key + packed row in shared
+//                  memory, compacted per range.
+//                  phase 2 once the tile's look-back is done: patch the one job
+//                  per range that began before the range, then copy the parked
+//                  rows to their final position in global memory
 //   scan warp      event loop: (a) as soon as phase 1 of a tile is complete,
 //                  publish its aggregate (job count + summary of the job left
 //                  open at its end) — this never waits on another CTA;
@@ -33,61 +40,78 @@ constexpr int kThreads = kWorkers + 64;
 constexpr int kStages = 3;
 constexpr uint64_t kWatchdogNs = 8000000000ull; // a stuck wait traps instead of hanging the GPU
 
-struct __align__(16) ChunkMasks {
-  uint32_t head, tail, he, term; // bit b = record 32*chunk + b of the tile
-  uint32_t fail, err, pad0, pad1;
+// What a worker warp leaves behind for its range of the tile.
+struct __align__(8) RangeInfo {
+  uint64_t suffix; // summary of the job still open at the end of the range (restricted to the range)
+  uint64_t unres;  // summary of the range's first job when it began before the range
+  uint32_t count;  // jobs ending in the range
+  uint32_t flags;
+  uint32_t has_unres; // set by the lane that parked `unres`
+  uint32_t pad;
 };
+enum : uint32_t { RANGE_CLOSED = 1u, RANGE_FIRST_IS_HEAD = 4u };
+
+// Parked row (phase 1 -> phase 2): Summ.f[0,16) | job already finished at its first record[16] |
+// winner index within the tile[17,..)
+constexpr uint32_t kParkedFin0 = 1u << 16;
+constexpr uint32_t kVerdictMask = 0x1FFFFu;
 
 template <int TILE> struct __align__(128) StageBuf {
   // keyx[1] = key of the record before the tile, keyx[2..TILE+1] = the tile's
-  // keys (16-byte aligned for the bulk copy), keyx[TILE+2] = key after the tile
+  // keys (16-byte aligned for the bulk copy), keyx[TILE+2] = key after the tile.
+  // Phase 1 compacts the keys of each range's job-ending records in place.
   uint64_t keyx[TILE + 4];
   uint16_t reason[TILE];
   uint8_t kind[TILE];
   uint8_t flags[TILE];
   uint8_t stage[TILE];
-  uint8_t code[TILE]; // LUT code per record (phase 1 -> phase 2)
-  ChunkMasks masks[TILE / 32];
-  uint32_t chunk_off[TILE / 32]; // jobs ending before each chunk, tile-local
-  uint64_t carry;                // summary carried into the tile's first job
-  uint64_t local_summ;           // summary of the job left open at the tile's end
-  uint32_t local_count;          // jobs ending in the tile
-  uint32_t tile_base;            // job rows before the tile
-  int32_t tile;                  // tile id, -1 = end of work
+  uint32_t packed[TILE]; // parked rows, compacted per range like the keys
+  RangeInfo range[kWorkerWarps];
+  uint32_t range_off[kWorkerWarps]; // jobs ending before each range, tile-local
+  uint64_t carry;                   // summary carried into the tile's first job
+  uint64_t local_summ;              // summary of the job left open at the tile's end
+  uint32_t local_count;             // jobs ending in the tile
+  uint32_t tile_base;               // job rows before the tile
+  int32_t tile;                     // tile id, -1 = end of work
 };
+
+// Verdict table entry = packed verdict of the record plus the fold bits above it.
+constexpr uint32_t VT_HE = 1u << 17, VT_TERM = 1u << 18, VT_FAIL = 1u << 19, VT_ERR = 1u << 20;
 
 struct Ctl {
   uint64_t full[kStages];   // tile landed            (producer -> workers)
   uint64_t p1done[kStages]; // phase 1 complete       (workers -> scan warp)
   uint64_t lbdone[kStages]; // look-back complete     (scan warp -> workers)
   uint64_t freeb[kStages];  // phase 2 complete       (workers -> producer)
-  uint32_t appl[8];         // applied_verdict(action)
-  uint8_t lut[128];         // (kind, reason) -> code
+  uint32_t vt[1024];        // [gate class 0..3][code 0..255] -> verdict | fold bits
+  uint8_t lut[128];         // (kind, reason) -> code (action | cause_tpl << 3 | msg_tpl << 5)
+  uint16_t lut2[128];       // (flags & 7) | stage << 3 -> 256 * gate class (0 dropped, 1 no checkpoint, 2 finished, 3 apply)
 };
 
 // Tile descriptor: two self-validating 64-bit words, each published with one
 // relaxed store, so no fence is needed on either side.
-//   c: count[0,32) | status[32,34) | generation[34,43)
-//   s: win_idx[0,32) | Summ.f[32,53) | status[53,55) | generation[55,64)
+//   c: count[0,32) | status[32,34) | generation[34,41)
+//   s: win_idx[0,32) | Summ.f[32,55) | status[55,57) | generation[57,64)
 struct __align__(16) TileDesc {
   uint64_t c, s;
 };
 enum : uint32_t { DESC_INVALID = 0, DESC_AGG = 1, DESC_INC = 2 };
-constexpr uint32_t kGenMax = 511;
+constexpr uint32_t kGenMax = 127;
+constexpr uint32_t kSummFMask = (1u << F_BITS) - 1u;
 __host__ __device__ __forceinline__ uint64_t desc_c(uint32_t count, uint32_t status, uint32_t gen) {
   return (uint64_t)count | (uint64_t)status << 32 | (uint64_t)gen << 34;
 }
 __host__ __device__ __forceinline__ uint64_t desc_s(Summ sm, uint32_t status, uint32_t gen) {
-  return (uint64_t)sm.win_idx | (uint64_t)(sm.f & 0x1FFFFFu) << 32 | (uint64_t)status << 53 | (uint64_t)gen << 55;
+  return (uint64_t)sm.win_idx | (uint64_t)(sm.f & kSummFMask) << 32 | (uint64_t)status << 55 | (uint64_t)gen << 57;
 }
 __host__ __device__ __forceinline__ uint32_t desc_c_status(uint64_t c, uint32_t gen) {
-  return ((uint32_t)(c >> 34) & 511u) == gen ? (uint32_t)(c >> 32) & 3u : DESC_INVALID;
+  return ((uint32_t)(c >> 34) & 127u) == gen ? (uint32_t)(c >> 32) & 3u : DESC_INVALID;
 }
 __host__ __device__ __forceinline__ uint32_t desc_s_status(uint64_t s, uint32_t gen) {
-  return (uint32_t)(s >> 55) == gen ? (uint32_t)(s >> 53) & 3u : DESC_INVALID;
+  return (uint32_t)(s >> 57) == gen ? (uint32_t)(s >> 55) & 3u : DESC_INVALID;
 }
 __host__ __device__ __forceinline__ Summ desc_s_summ(uint64_t s) {
-  return Summ{(uint32_t)s, (uint32_t)(s >> 32) & 0x1FFFFFu};
+  return Summ{(uint32_t)s, (uint32_t)(s >> 32) & kSummFMask};
 }
 
 struct ClassifyParams {
@@ -108,10 +132,14 @@ struct ClassifyParams {
   uint32_t term_mask; // bit a: new_stage_of(a) is a finished stage
   uint32_t gen;
   uint8_t lut[128];
+#ifdef NXS_TRACE
+  unsigned long long *trace; // [0] = number of events, then (time, cta<<40 | event<<32 | tile) pairs
+  uint32_t trace_cap;
+#endif
 };
 
 template <int TILE> constexpr size_t classify_smem_bytes() {
-  return sizeof(StageBuf<TILE>) * kStages + sizeof(Ctl) + 128;
+  return sizeof(StageBuf<TILE>) * kStages + sizeof(Ctl);
 }
 
 #if defined(__CUDACC__)
@@ -127,12 +155,28 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
 }
 __device__ __forceinline__ void named_barrier_workers() { asm volatile("bar.sync 1, %0;" ::"n"(kWorkers) : "memory"); }
 
+#ifdef NXS_TRACE
+// Debug build only: CTAs 0, 97 and 211 log pipeline events with the global timer.
+enum : uint32_t { EV_CLAIM = 1, EV_ISSUED, EV_P1_START, EV_P1_END, EV_AGG_START, EV_AGG_END, EV_LB_START, EV_LB_END,
+                  EV_P2_START, EV_P2_END, EV_LB_POLL };
+__device__ __forceinline__ void trace_event(const ClassifyParams &p, uint32_t ev, uint32_t tile) {
+  if (!p.trace || !(blockIdx.x == 0 || blockIdx.x == 97 || blockIdx.x == 211)) return;
+  const unsigned long long i = atomicAdd(p.trace, 1ull);
+  if (i >= p.trace_cap) return;
+  p.trace[1 + 2 * i] = global_timer_ns();
+  p.trace[2 + 2 * i] = (unsigned long long)blockIdx.x << 40 | (unsigned long long)ev << 32 | tile;
+}
+#define NXS_TRACE_EVENT(p, ev, tile) trace_event(p, ev, tile)
+#else
+#define NXS_TRACE_EVENT(p, ev, tile) ((void)0)
+#endif
+
 struct Watchdog {
   uint64_t t0;
   uint32_t spins;
   __device__ __forceinline__ Watchdog() : t0(0), spins(0) {}
   __device__ __forceinline__ void tick(uint32_t *flag) {
-    if ((++spins & 4095u) == 0) {
+    if ((++spins & 63u) == 0) {
       const uint64_t now = global_timer_ns();
       if (t0 == 0) t0 = now;
       else if (now - t0 > kWatchdogNs) {
@@ -152,7 +196,7 @@ __device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<
   for (uint32_t k = 0;; ++k) {
     const uint32_t s = k % kStages, use = k / kStages;
     if (use > 0) {
-      while (!mbar_try_wait(&ctl.freeb[s], (use - 1) & 1u)) wd.tick(p.counters + 2);
+      while (!mbar_try_wait(&ctl.freeb[s], (use - 1) & 1u, 20000u)) wd.tick(p.counters + 2);
       wd.reset();
     }
     StageBuf<TILE> &sb = stages[s];
@@ -163,6 +207,7 @@ __device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<
       mbar_arrive_n(bar, 2);
       break;
     }
+    NXS_TRACE_EVENT(p, EV_CLAIM, id);
     next = atomicAdd(p.counters, 1u); // consumed one iteration later: latency hidden
     sb.tile = (int32_t)id;
     const uint32_t start = id * TILE;
@@ -176,6 +221,7 @@ __device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<
       if (start > 0) cp_async_8(&sb.keyx[1], p.key + start - 1);
       if (start + TILE < p.n) cp_async_8(&sb.keyx[2 + TILE], p.key + start + TILE);
       mbar_arrive_after_cp_async(bar);
+      NXS_TRACE_EVENT(p, EV_ISSUED, id);
     } else {
       mbar_arrive_n(bar, 2); // ragged last tile: the workers load it themselves
     }
@@ -189,10 +235,18 @@ __device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<
 }
 
 // ---------------------------------------------------------------------- workers
+__device__ __forceinline__ Summ shfl_summ(Summ s, int src) {
+  return Summ{__shfl_sync(0xffffffffu, s.win_idx, src), __shfl_sync(0xffffffffu, s.f, src)};
+}
+__device__ __forceinline__ Summ shfl_down_summ(Summ s, int d) {
+  return Summ{__shfl_down_sync(0xffffffffu, s.win_idx, d), __shfl_down_sync(0xffffffffu, s.f, d)};
+}
+
 template <int TILE, bool FULL>
 __device__ __forceinline__ void phase1(const ClassifyParams &p, StageBuf<TILE> &sb, const Ctl &ctl, uint32_t tile,
                                        uint32_t warp, uint32_t lane) {
-  constexpr int CHUNKS = TILE / 32;
+  constexpr uint32_t RANGE = TILE / kWorkerWarps; // records per warp
+  constexpr uint32_t CPW = RANGE / 32;            // 32-record chunks per warp
   const uint32_t start = tile * TILE;
   const uint32_t cnt = FULL ? (uint32_t)TILE : p.n - start;
   if (!FULL) { // ragged tile: guarded loads by the worker warps, then a worker-only barrier
@@ -206,85 +260,134 @@ __device__ __forceinline__ void phase1(const ClassifyParams &p, StageBuf<TILE> &
     if (warp == 0 && lane == 0 && start > 0) sb.keyx[1] = p.key[start - 1];
     named_barrier_workers();
   }
-  const bool first_tile = start == 0;
+  const uint32_t r0 = warp * RANGE;
+  if (!FULL && r0 >= cnt) { // nothing of the ragged tile falls in this range
+    if (lane == 0) sb.range[warp] = RangeInfo{summ_pack(summ_identity()), 0ull, 0u, 0u, 0u, 0u};
+    return;
+  }
   const bool last_tile = start + cnt == p.n;
-  const uint32_t fin = p.finished_mask, tmask = p.term_mask;
-#pragma unroll 2
-  for (uint32_t c = warp; c < (uint32_t)CHUNKS; c += kWorkerWarps) {
-    const uint32_t i = c * 32 + lane;
-    bool head = false, tail = false, he = false, term = false, fail = false, err = false;
-    if (FULL || i < cnt) {
+  const uint32_t gbase = p.record_base + start;
+  const uint32_t le = (2u << lane) - 1u, lt = le >> 1;
+  // Does the first record of the range begin a job?  (warp-uniform)
+  uint32_t prev_bit = (r0 == 0 && start == 0) ? 1u : (uint32_t)(sb.keyx[2 + r0] != sb.keyx[1 + r0]);
+  const uint32_t first_is_head = prev_bit;
+  Summ ctx = summ_identity(); // the job left open by the records of this range seen so far
+  uint32_t wcount = 0, closed = 0;
+  if (lane == 0) sb.range[warp].has_unres = 0;
+  __syncwarp();
+
+#pragma unroll
+  for (uint32_t j = 0; j < CPW; ++j) {
+    const uint32_t i = r0 + j * 32 + lane;
+    const bool valid = FULL || i < cnt;
+    uint32_t st = 0, vt = 0, code = 0;
+    uint64_t key = 0;
+    bool tail = false;
+    if (valid) {
       const uint32_t kind = sb.kind[i], reason = sb.reason[i], fl = sb.flags[i];
-      const uint32_t st = sb.stage[i] & 15u;
-      const uint64_t key = sb.keyx[2 + i], pk = sb.keyx[1 + i], nk = sb.keyx[3 + i];
-      head = (key != pk) || (first_tile && i == 0);
-      tail = (key != nk) || (last_tile && i == cnt - 1);
-      // onEvent: guards (:155,:161,:218) then the (kind, reason) switch arms
-      const uint32_t idx = min(kind, 3u) * 32u + (reason < 32u ? reason : 0u);
-      const uint32_t code = ((fl & 3u) == 3u) ? ctl.lut[idx] : 0u;
-      const uint32_t a = code & 7u;
-      // superviseAction: no checkpoint (:265) -> finished (:276) -> switch (:283)
-      const bool exists = (fl & NXS_FLAG_CHECKPOINT) != 0;
-      const bool finished = (fin >> st) & 1u;
-      const uint32_t base = exists ? (finished ? (a | 1u << 14) : ctl.appl[a])
-                                   : (a | 1u << 12 | NXS_ERR_NO_CHECKPOINT << 15);
-      const uint32_t v = a ? (base | (code >> 3) << 9) : 0u;
-      __stcs(p.verdict + start + i, v);
-      sb.code[i] = (uint8_t)code;
-      he = a != 0 && exists;
-      err = a != 0 && !exists;
-      term = he && ((tmask >> a) & 1u);
-      fail = he && a != NXS_ACTION_RUNNING;
+      st = sb.stage[i] & 15u;
+      key = sb.keyx[2 + i];
+      const uint64_t nk = sb.keyx[3 + i];
+      tail = key != nk;
+      if (last_tile && i == cnt - 1) tail = true;
+      // onEvent: guards (:155,:161,:218) and the (kind, reason) switch arms, then superviseAction's
+      // order: no checkpoint (:265) -> finished (:276) -> switch (:283).  All three are table lookups.
+      code = ctl.lut[min(kind, 3u) * 32u + (reason < 32u ? reason : 0u)];
+      vt = ctl.vt[ctl.lut2[(fl & 7u) | st << 3] + code];
+      __stcs(p.verdict + start + i, vt & kVerdictMask);
     }
-    ChunkMasks m;
-    m.head = __ballot_sync(0xffffffffu, head);
-    m.tail = __ballot_sync(0xffffffffu, tail);
-    m.he = __ballot_sync(0xffffffffu, he);
-    m.term = __ballot_sync(0xffffffffu, term);
-    m.fail = __ballot_sync(0xffffffffu, fail);
-    m.err = __ballot_sync(0xffffffffu, err);
-    m.pad0 = m.pad1 = 0;
-    if (lane == 0) sb.masks[c] = m;
+    const uint32_t T = __ballot_sync(0xffffffffu, tail);
+    const uint32_t H = T << 1 | prev_bit; // bit b: record b of the chunk begins a job
+    prev_bit = T >> 31;
+    const uint32_t HE = ballot_bit(vt, VT_HE), TM = ballot_bit(vt, VT_TERM);
+    const uint32_t FL = ballot_bit(vt, VT_FAIL), ER = ballot_bit(vt, VT_ERR);
+
+    // fold of the records from the job's first record in this chunk (or the chunk start) up to this lane
+    const uint32_t h_in = H & le;
+    const uint32_t hb = hi_bit(h_in | 1u); // h_in == 0 -> 0: the run starts at the chunk start
+    const uint32_t seg = le & (~0u << hb);
+    const uint32_t hes = HE & seg, tms = TM & seg;
+    const uint32_t upto = tms ^ (tms - 1u); // through the first stop; all ones when there is none
+    const uint32_t app = hes & upto;        // applied records (under the premise)
+    const uint32_t wm = app & FL;           // ... with a failure action
+    const uint32_t wp = hi_bit(wm | 1u);    // the winner: the last of them
+    const uint32_t code_w = __shfl_sync(0xffffffffu, code, wp);
+    const uint32_t st_head = __shfl_sync(0xffffffffu, st, hb);
+    uint32_t f = 0;
+    if (ER & seg) f |= F_ERR;
+    if (tms) f |= F_STOPPED;
+    if (hes & ~upto) f |= F_SKIP;
+    if (hes) f |= F_HAS_APP | NXS_ACTION_RUNNING; // a non-failure handled record is a ToRunning
+    if (wm) {
+      f |= F_HAS_WIN | (code_w >> 3) << F_WIN_SHIFT;
+      if ((app >> wp) == 1u) f = (f & ~F_ALAST_MASK) | (code_w & 7u); // nothing applied after the winner
+    }
+    Summ S{gbase + r0 + j * 32 + wp, f};
+    if (h_in) S.f |= st_head << F_S0_SHIFT | F_ANCHORED; // the job begins in this chunk
+    else S = summ_combine(ctx, S);                        // it continues the job left open before the chunk
+
+    __syncwarp(); // every lane has read its keys: compaction may overwrite them now
+    if (tail) {
+      const uint32_t slot = r0 + wcount + __popc(T & lt);
+      sb.keyx[2 + slot] = key;
+      if (S.f & F_ANCHORED) {
+        const uint32_t fin0 = (p.finished_mask >> ((S.f >> F_S0_SHIFT) & 15u)) & 1u;
+        sb.packed[slot] = (S.f & 0xFFFFu) | fin0 << 16 | (S.win_idx - gbase) << 17;
+      } else { // only the first job of a range can have begun before it
+        sb.range[warp].unres = summ_pack(S);
+        sb.range[warp].has_unres = 1;
+      }
+    }
+    wcount += __popc(T);
+    if (FULL || r0 + j * 32 + 31 < cnt) closed = T >> 31;
+    else if (last_tile) closed = 1; // the ragged tile ends inside this chunk: its last record closes a job
+    ctx = shfl_summ(S, 31);
+  }
+  __syncwarp();
+  if (lane == 0) {
+    sb.range[warp].suffix = summ_pack(ctx);
+    sb.range[warp].count = wcount;
+    sb.range[warp].flags = (closed ? RANGE_CLOSED : 0u) | (first_is_head ? RANGE_FIRST_IS_HEAD : 0u);
   }
 }
 
 template <int TILE>
 __device__ __forceinline__ void phase2(const ClassifyParams &p, const StageBuf<TILE> &sb, uint32_t warp,
                                        uint32_t lane) {
-  constexpr int CHUNKS = TILE / 32;
-  const uint32_t start = (uint32_t)sb.tile * TILE;
-  const uint32_t tile_base = sb.tile_base;
-  const Summ carry = summ_unpack(sb.carry);
-  const uint32_t le = (2u << lane) - 1u;
-  for (uint32_t c = warp; c < (uint32_t)CHUNKS; c += kWorkerWarps) {
-    const ChunkMasks m = sb.masks[c];
-    if (!((m.tail >> lane) & 1u)) continue;
-    const uint32_t pos = tile_base + sb.chunk_off[c] + __popc(m.tail & (le >> 1));
-    // first record of this job: nearest head at or before this lane
-    uint32_t cc = c, hm = m.head & le;
-    while (hm == 0 && cc > 0) {
-      --cc;
-      hm = sb.masks[cc].head;
+  constexpr uint32_t RANGE = TILE / kWorkerWarps;
+  const uint32_t count = sb.range[warp].count;
+  if (count == 0) return;
+  const uint32_t r0 = warp * RANGE;
+  const uint32_t gbase = p.record_base + (uint32_t)sb.tile * TILE;
+  nxs_job_row *rows = p.rows + sb.tile_base + sb.range_off[warp];
+  uint32_t first = 0;
+  if (sb.range[warp].has_unres) { // the range's first job began before the range: gather what came before
+    if (lane == 0) {
+      Summ acc = summ_identity();
+      bool anchored = false;
+      for (int w = (int)warp - 1; w >= 0 && !anchored; --w) {
+        const Summ sfx = summ_unpack(sb.range[w].suffix);
+        acc = summ_combine(sfx, acc);
+        anchored = (sfx.f & F_ANCHORED) != 0;
+      }
+      if (!anchored) acc = summ_combine(summ_unpack(sb.carry), acc);
+      uint32_t verdict, winner;
+      summ_resolve(summ_combine(acc, summ_unpack(sb.range[warp].unres)), p.finished_mask, verdict, winner);
+      const uint64_t key = sb.keyx[2 + r0];
+      __stcs(reinterpret_cast<uint4 *>(rows), make_uint4((uint32_t)key, (uint32_t)(key >> 32), verdict, winner));
     }
-    uint32_t hbit = 0;
-    Summ S = carry; // no head in the tile before this record: the job began earlier
-    if (hm) {
-      hbit = hi_bit(hm);
-      S = summ_anchor(sb.stage[cc * 32 + hbit]);
-    }
-    for (uint32_t k = cc; k <= c; ++k) {
-      uint32_t mk = ~0u;
-      if (k == cc) mk <<= hbit;
-      if (k == c) mk &= le;
-      const ChunkMasks w = sb.masks[k];
-      S = summ_combine(S, summ_piece(w.he & mk, w.term & mk, w.fail & mk, w.err & mk, sb.code, k * 32,
-                                     p.record_base + start));
-    }
-    uint32_t verdict, winner;
-    summ_resolve(S, p.finished_mask, verdict, winner);
-    const uint64_t key = sb.keyx[2 + c * 32 + lane];
-    __stcs(reinterpret_cast<uint4 *>(p.rows + pos),
-           make_uint4((uint32_t)key, (uint32_t)(key >> 32), verdict, winner));
+    first = 1;
+  }
+  for (uint32_t j = first + lane; j < count; j += 32) {
+    const uint64_t key = sb.keyx[2 + r0 + j];
+    const uint32_t pk = sb.packed[r0 + j];
+    // close the job (summ_resolve on the parked fields)
+    const bool fin0 = (pk & kParkedFin0) != 0;
+    uint32_t v = fin0 ? (((pk & F_HAS_APP) ? F_SKIP : 0u) | (pk & F_ERR))
+                      : ((pk & F_VERDICT_MASK) | new_stage_of(pk & F_ALAST_MASK) << 3);
+    v |= (pk & F_ERR) >> 3;
+    const uint32_t winner = (!fin0 && (pk & F_HAS_WIN)) ? gbase + (pk >> 17) : NXS_NO_WINNER;
+    __stcs(reinterpret_cast<uint4 *>(rows + j), make_uint4((uint32_t)key, (uint32_t)(key >> 32), v, winner));
   }
 }
 
@@ -296,117 +399,77 @@ __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TI
   bool end = false;
   Watchdog wd;
   while (true) {
-    bool progressed = false;
-    if (!end && __all_sync(0xffffffffu, mbar_test_wait(&ctl.full[s1], par1))) {
+    // Phase 1 of a landed tile comes first (it feeds the aggregate every later tile waits for); a warp
+    // with nothing to fold sleeps on the barrier it needs next instead of polling.
+    bool landed = false;
+    if (!end) {
+      const bool p2_pending = k2 < k1;
+      landed = __all_sync(0xffffffffu, p2_pending ? mbar_test_wait(&ctl.full[s1], par1)
+                                                  : mbar_try_wait(&ctl.full[s1], par1, 2000u));
+    }
+    if (landed) {
       StageBuf<TILE> &sb = stages[s1];
       const int32_t t = sb.tile;
       if (t < 0) {
         end = true;
       } else {
+        if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_START, (uint32_t)t);
         if (p.n - (uint32_t)t * TILE >= (uint32_t)TILE) phase1<TILE, true>(p, sb, ctl, (uint32_t)t, warp, lane);
         else phase1<TILE, false>(p, sb, ctl, (uint32_t)t, warp, lane);
+        if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_END, (uint32_t)t);
         ++k1;
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&ctl.p1done[s1]);
       if (++s1 == kStages) s1 = 0, par1 ^= 1u;
-      progressed = true;
+      wd.reset();
+      continue;
     }
-    if (!progressed && k2 < k1 && __all_sync(0xffffffffu, mbar_test_wait(&ctl.lbdone[s2], par2))) {
-      phase2<TILE>(p, stages[s2], warp, lane);
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&ctl.freeb[s2]);
-      ++k2;
-      if (++s2 == kStages) s2 = 0, par2 ^= 1u;
-      progressed = true;
+    if (k2 < k1) {
+      if (__all_sync(0xffffffffu, mbar_try_wait(&ctl.lbdone[s2], par2, end ? 2000u : 300u))) {
+        if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P2_START, (uint32_t)stages[s2].tile);
+        phase2<TILE>(p, stages[s2], warp, lane);
+        if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P2_END, (uint32_t)stages[s2].tile);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&ctl.freeb[s2]);
+        ++k2;
+        if (++s2 == kStages) s2 = 0, par2 ^= 1u;
+        wd.reset();
+        continue;
+      }
+    } else if (end) {
+      break;
     }
-    if (end && k2 == k1) break;
-    if (progressed) wd.reset();
-    else wd.tick(p.counters + 2);
+    wd.tick(p.counters + 2);
   }
 }
 
 // -------------------------------------------------------------------- scan warp
-__device__ __forceinline__ Summ shfl_summ(Summ s, int src) {
-  return Summ{__shfl_sync(0xffffffffu, s.win_idx, src), __shfl_sync(0xffffffffu, s.f, src)};
-}
-__device__ __forceinline__ Summ shfl_down_summ(Summ s, int d) {
-  return Summ{__shfl_down_sync(0xffffffffu, s.win_idx, d), __shfl_down_sync(0xffffffffu, s.f, d)};
-}
-
-// Tile-local job count, per-chunk row offsets and the summary of the job left
+// Tile-local job count, per-range row offsets and the summary of the job left
 // open at the end of the tile; publishes the tile's aggregate descriptor.
 template <int TILE>
 __device__ __forceinline__ void aggregate_tile(const ClassifyParams &p, StageBuf<TILE> &sb, uint32_t tile,
                                                uint32_t lane) {
-  constexpr int CHUNKS = TILE / 32;
-  constexpr int CPL = CHUNKS / 32; // chunks per lane
-  static_assert(CHUNKS % 32 == 0, "TILE must be a multiple of 1024");
-  const uint32_t start = tile * TILE;
-  const uint32_t cnt = min((uint32_t)TILE, p.n - start);
-
-  uint32_t tails[CPL], running = 0;
-  int last_head = -1;
+  const uint32_t mine = lane < (uint32_t)kWorkerWarps ? sb.range[lane].count : 0u;
+  uint32_t incl = mine;
 #pragma unroll
-  for (int j = 0; j < CPL; ++j) {
-    const uint32_t c = lane * CPL + j;
-    const uint32_t t = sb.masks[c].tail, h = sb.masks[c].head;
-    tails[j] = __popc(t);
-    running += tails[j];
-    if (h) last_head = (int)(c * 32 + hi_bit(h));
-  }
-  uint32_t incl = running;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
+  for (int d = 1; d < kWorkerWarps; d <<= 1) {
     const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
     if ((int)lane >= d) incl += o;
   }
-  uint32_t off = incl - running;
-#pragma unroll
-  for (int j = 0; j < CPL; ++j) {
-    sb.chunk_off[lane * CPL + j] = off;
-    off += tails[j];
-  }
-  const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) last_head = max(last_head, __shfl_xor_sync(0xffffffffu, last_head, d));
-
-  const uint32_t last = cnt - 1;
-  const bool closed = (sb.masks[last >> 5].tail >> (last & 31)) & 1u;
-  Summ T{0u, F_ANCHORED}; // closed: nothing flows into the next tile
-  if (!closed) {          // warp-uniform
-    const uint32_t from = last_head < 0 ? 0u : (uint32_t)last_head;
-    const uint32_t c_from = from >> 5, c_last = last >> 5;
-    Summ S = summ_identity();
-    if (c_last - c_from < 2) { // usual case: the open job began in the last two chunks; every lane computes it
-      for (uint32_t c = c_from; c <= c_last; ++c) {
-        uint32_t mk = ~0u;
-        if (c == c_from) mk <<= (from & 31);
-        const ChunkMasks w = sb.masks[c];
-        S = summ_combine(S, summ_piece(w.he & mk, w.term & mk, w.fail & mk, w.err & mk, sb.code, c * 32,
-                                       p.record_base + start));
-      }
-    } else { // long open job: pieces per lane, then an ordered warp reduction
-#pragma unroll
-      for (int j = 0; j < CPL; ++j) {
-        const uint32_t c = lane * CPL + j;
-        if (c < c_from) continue;
-        uint32_t mk = ~0u;
-        if (c == c_from) mk <<= (from & 31);
-        const ChunkMasks w = sb.masks[c];
-        S = summ_combine(S, summ_piece(w.he & mk, w.term & mk, w.fail & mk, w.err & mk, sb.code, c * 32,
-                                       p.record_base + start));
-      }
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const Summ o = shfl_down_summ(S, d);
-        if ((int)lane + d < 32) S = summ_combine(S, o);
-      }
-      S = shfl_summ(S, 0);
-    }
-    T = last_head < 0 ? S : summ_combine(summ_anchor(sb.stage[from]), S);
-  }
+  if (lane < (uint32_t)kWorkerWarps) sb.range_off[lane] = incl - mine;
+  const uint32_t total = __shfl_sync(0xffffffffu, incl, kWorkerWarps - 1);
   if (lane == 0) {
+    // the job open at the tile's end: walk the ranges from the right until one holds its first record
+    Summ T = summ_identity();
+    for (int w = kWorkerWarps - 1; w >= 0; --w) {
+      if (sb.range[w].flags & RANGE_CLOSED) { // (everything right of a closed range is empty)
+        T = Summ{0u, F_ANCHORED};             // nothing flows into the next tile
+        break;
+      }
+      T = summ_combine(summ_unpack(sb.range[w].suffix), T);
+      if (T.f & F_ANCHORED) break;
+    }
     sb.local_count = total;
     sb.local_summ = summ_pack(T);
     if (tile == 0) {
@@ -427,38 +490,51 @@ struct LookbackState {
   bool summ_done;   // an anchored summary has been reached (or none is needed)
 };
 
-// One non-blocking look-back step over up to 32 predecessor descriptors.
-// Returns true when both walks are complete.  A window is consumed only when
-// every descriptor it needs has been published; otherwise nothing changes.
+// One non-blocking look-back step.  The warp reads kLookbackWindows x 32 predecessor descriptors
+// in one round trip (the loads are independent, so they cost one latency) and consumes them 32 at
+// a time, nearest first.  A window is consumed only when every descriptor it needs has been
+// published; otherwise the walk stops there and the next poll resumes from it.  Returns true when
+// both walks (job count, carried summary) are complete.
+// Why several windows per round trip: tiles are published at up to ~100 per microsecond, and a walk
+// that advanced only 32 tiles per L2 round trip could never catch up with the newest inclusive tile.
+constexpr int kLookbackWindows = 8;
 __device__ __forceinline__ bool lookback_poll(const ClassifyParams &p, LookbackState &st, uint32_t lane) {
-  const int idx = st.pos - (int)lane;
-  const bool valid = idx >= 0;
-  uint64_t c = 0, s = 0;
-  if (valid) ld_desc(p.desc + idx, c, s);
-  const uint32_t cs = desc_c_status(c, p.gen), ss = desc_s_status(s, p.gen);
-  const Summ mine = desc_s_summ(s);
-  const uint32_t m_valid = __ballot_sync(0xffffffffu, valid);
-  const uint32_t m_cok = __ballot_sync(0xffffffffu, valid && cs != DESC_INVALID);
-  const uint32_t m_cinc = __ballot_sync(0xffffffffu, valid && cs == DESC_INC);
-  const uint32_t m_sok = __ballot_sync(0xffffffffu, valid && ss != DESC_INVALID);
-  const uint32_t m_sanch = __ballot_sync(0xffffffffu, valid && ss != DESC_INVALID && (mine.f & F_ANCHORED));
-  const uint32_t need_c = st.count_done ? 0u : (m_cinc ? (2u << lo_bit(m_cinc)) - 1u : m_valid);
-  const uint32_t need_s = st.summ_done ? 0u : (m_sanch ? (2u << lo_bit(m_sanch)) - 1u : m_valid);
-  if ((need_c & ~m_cok) | (need_s & ~m_sok)) return false;
-  if (!st.count_done) {
-    uint32_t contrib = ((need_c >> lane) & 1u) ? (uint32_t)c : 0u;
+  uint64_t c[kLookbackWindows], s[kLookbackWindows];
 #pragma unroll
-    for (int d = 16; d > 0; d >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, d);
-    st.excl += contrib;
-    st.count_done = m_cinc != 0;
+  for (int k = 0; k < kLookbackWindows; ++k) {
+    const int idx = st.pos - (int)lane - 32 * k;
+    c[k] = 0;
+    s[k] = 0;
+    if (idx >= 0) ld_desc(p.desc + idx, c[k], s[k]);
   }
-  if (!st.summ_done) {
-    const uint32_t upto = hi_bit(need_s);
-    for (uint32_t j = 0; j <= upto; ++j) st.carry = summ_combine(shfl_summ(mine, (int)j), st.carry);
-    st.summ_done = m_sanch != 0;
+#pragma unroll
+  for (int k = 0; k < kLookbackWindows; ++k) {
+    const bool valid = st.pos - (int)lane >= 0;
+    const uint32_t cs = desc_c_status(c[k], p.gen), ss = desc_s_status(s[k], p.gen);
+    const Summ mine = desc_s_summ(s[k]);
+    const uint32_t m_valid = __ballot_sync(0xffffffffu, valid);
+    const uint32_t m_cok = __ballot_sync(0xffffffffu, valid && cs != DESC_INVALID);
+    const uint32_t m_cinc = __ballot_sync(0xffffffffu, valid && cs == DESC_INC);
+    const uint32_t m_sok = __ballot_sync(0xffffffffu, valid && ss != DESC_INVALID);
+    const uint32_t m_sanch = __ballot_sync(0xffffffffu, valid && ss != DESC_INVALID && (mine.f & F_ANCHORED));
+    const uint32_t need_c = st.count_done ? 0u : (m_cinc ? (2u << lo_bit(m_cinc)) - 1u : m_valid);
+    const uint32_t need_s = st.summ_done ? 0u : (m_sanch ? (2u << lo_bit(m_sanch)) - 1u : m_valid);
+    if ((need_c & ~m_cok) | (need_s & ~m_sok)) return false;
+    if (!st.count_done) {
+      uint32_t contrib = ((need_c >> lane) & 1u) ? (uint32_t)c[k] : 0u;
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, d);
+      st.excl += contrib;
+      st.count_done = m_cinc != 0;
+    }
+    if (!st.summ_done) {
+      const uint32_t upto = hi_bit(need_s);
+      for (uint32_t j = 0; j <= upto; ++j) st.carry = summ_combine(shfl_summ(mine, (int)j), st.carry);
+      st.summ_done = m_sanch != 0;
+    }
+    if (st.count_done && st.summ_done) return true;
+    st.pos -= 32;
   }
-  if (st.count_done && st.summ_done) return true;
-  st.pos -= 32;
   return false;
 }
 
@@ -470,19 +546,23 @@ __device__ __forceinline__ void scan_loop(const ClassifyParams &p, StageBuf<TILE
   LookbackState st{0, 0u, summ_identity(), false, false};
   Watchdog wd;
   while (true) {
-    bool progressed = false;
+    // Aggregates first: publishing one never waits on another CTA, and every later tile needs it.
     if (!end && __all_sync(0xffffffffu, mbar_test_wait(&ctl.p1done[sa], para))) {
       StageBuf<TILE> &sb = stages[sa];
       const int32_t t = sb.tile;
       if (t < 0) {
         end = true;
       } else {
+        if (lane == 0) NXS_TRACE_EVENT(p, EV_AGG_START, (uint32_t)t);
         aggregate_tile<TILE>(p, sb, (uint32_t)t, lane);
+        if (lane == 0) NXS_TRACE_EVENT(p, EV_AGG_END, (uint32_t)t);
         ++ka;
         if (++sa == kStages) sa = 0, para ^= 1u;
       }
-      progressed = true;
-    } else if (kl < ka) {
+      wd.reset();
+      continue;
+    }
+    if (kl < ka) { // a tile waits for its look-back: poll its predecessors (each poll is one L2 round trip)
       StageBuf<TILE> &sb = stages[sl];
       const uint32_t tile = (uint32_t)sb.tile;
       if (!lb_active) {
@@ -490,9 +570,11 @@ __device__ __forceinline__ void scan_loop(const ClassifyParams &p, StageBuf<TILE
         st.excl = 0;
         st.carry = summ_identity();
         st.count_done = tile == 0;
-        st.summ_done = tile == 0 || (sb.masks[0].head & 1u); // first record starts a job: nothing to carry
+        st.summ_done = tile == 0 || (sb.range[0].flags & RANGE_FIRST_IS_HEAD); // nothing to carry
         lb_active = true;
+        if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_START, tile);
       }
+      if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_POLL, tile);
       if ((st.count_done && st.summ_done) || lookback_poll(p, st, lane)) {
         if (lane == 0) {
           const Summ T = summ_unpack(sb.local_summ);
@@ -507,24 +589,29 @@ __device__ __forceinline__ void scan_loop(const ClassifyParams &p, StageBuf<TILE
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&ctl.lbdone[sl]);
+        if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_END, tile);
         lb_active = false;
         ++kl;
         if (++sl == kStages) sl = 0;
-        progressed = true;
+        wd.reset();
+        continue;
       }
+    } else if (end) {
+      break;
+    } else { // nothing pending: sleep until the workers finish phase 1 of the next tile
+      (void)__all_sync(0xffffffffu, mbar_try_wait(&ctl.p1done[sa], para, 2000u));
     }
-    if (end && kl == ka) break;
-    if (progressed) wd.reset();
-    else wd.tick(p.counters + 2);
+    wd.tick(p.counters + 2);
   }
 }
 
 template <int TILE>
-__global__ void __launch_bounds__(kThreads) classify_kernel(const __grid_constant__ ClassifyParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t *aligned = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
-  StageBuf<TILE> *stages = reinterpret_cast<StageBuf<TILE> *>(aligned);
-  Ctl &ctl = *reinterpret_cast<Ctl *>(aligned + sizeof(StageBuf<TILE>) * kStages);
+__global__ void __launch_bounds__(kThreads, 2) classify_kernel(const __grid_constant__ ClassifyParams p) {
+  // (no manual re-alignment: keeping the pointer derived from the array keeps it in the shared
+  // address space, so accesses compile to LDS/STS rather than generic loads)
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  StageBuf<TILE> *stages = reinterpret_cast<StageBuf<TILE> *>(smem_raw);
+  Ctl &ctl = *reinterpret_cast<Ctl *>(smem_raw + sizeof(StageBuf<TILE>) * kStages);
   const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   if (tid == 0) {
@@ -536,8 +623,22 @@ __global__ void __launch_bounds__(kThreads) classify_kernel(const __grid_constan
     }
     mbar_fence_init();
   }
-  if (tid < 128) ctl.lut[tid] = p.lut[tid];
-  if (tid < 8) ctl.appl[tid] = (tid >= 1 && tid <= 4) ? applied_verdict(tid) : 0u;
+  if (tid < 128) {
+    ctl.lut[tid] = p.lut[tid];
+    const uint32_t fl = tid & 7u, st = tid >> 3;
+    ctl.lut2[tid] = (uint16_t)(256u * ((fl & 3u) != 3u ? 0u : !(fl & NXS_FLAG_CHECKPOINT) ? 1u : ((p.finished_mask >> st) & 1u) ? 2u : 3u));
+  }
+  for (uint32_t e = tid; e < 1024; e += kThreads) {
+    const uint32_t g = e >> 8, code = e & 255u, a = code & 7u, msg = code >> 5;
+    uint32_t v = 0;
+    if (g != 0 && a >= 1 && a <= 4) {
+      const uint32_t fold = VT_HE | (((p.term_mask >> a) & 1u) ? VT_TERM : 0u) | (a != NXS_ACTION_RUNNING ? VT_FAIL : 0u);
+      if (g == 1) v = a | msg << 9 | 1u << 12 | NXS_ERR_NO_CHECKPOINT << 15 | VT_ERR; // :265-273
+      else if (g == 2) v = a | msg << 9 | 1u << 14 | fold;                             // :276-279
+      else v = applied_verdict(a) | msg << 9 | fold;                                    // :283-370
+    }
+    ctl.vt[e] = v;
+  }
   __syncthreads(); // the only CTA-wide barrier
 
   if (warp < (uint32_t)kWorkerWarps) worker_loop<TILE>(p, stages, ctl, warp, lane);

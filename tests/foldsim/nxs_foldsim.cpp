@@ -62,7 +62,7 @@ extern "C" int nxs_foldsim(const uint8_t *kind, const uint16_t *reason, const ui
         const bool finished = (finished_mask >> st) & 1u;
         const uint32_t base = exists ? (finished ? (a | 1u << 14) : (a ? applied_verdict(a) : 0u))
                                      : (a | 1u << 12 | NXS_ERR_NO_CHECKPOINT << 15);
-        verdict[g] = a ? (base | (cd >> 3) << 9) : 0u;
+        verdict[g] = a ? (base | (cd >> 5) << 9) : 0u;
         code[i] = (uint8_t)cd;
         const bool he = a != 0 && exists;
         m.head |= (uint32_t)head << lane;
