@@ -27,6 +27,7 @@ struct nxs_ctx {
   uint32_t gen = 0;
   uint64_t launches = 0;
   uint8_t lut[128];
+  uint8_t code[8];
   // staging for the host-pointer entry point (allocated on first use)
   uint64_t staged_records = 0;
   uint8_t *d_in = nullptr;
@@ -117,7 +118,7 @@ int nxs_create(int device, uint64_t max_records, uint16_t finished_mask, nxs_ctx
   ctx->finished_mask = finished_mask;
   for (uint32_t a = 1; a <= 4; ++a)
     if ((finished_mask >> new_stage_of(a)) & 1u) ctx->term_mask |= 1u << a;
-  nxs_build_lut(ctx->lut);
+  nxs_build_lut(ctx->lut, ctx->code);
   int rc = NXS_OK;
   auto bail = [&](int code) {
     nxs_destroy(ctx);
@@ -135,6 +136,9 @@ int nxs_create(int device, uint64_t max_records, uint16_t finished_mask, nxs_ctx
   else if (ctx->tile == 4096) rc = configure_variant<4096>(ctx);
   else rc = NXS_ERR_ARG;
   if (rc != NXS_OK) return bail(rc);
+  if (getenv("NXS_VERBOSE"))
+    fprintf(stderr, "nxs: device %d, %d SMs, tile %d records, %d resident CTAs/SM x %d threads\n", device,
+            ctx->num_sms, ctx->tile, ctx->ctas_per_sm, kThreads);
   if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) return bail(NXS_ERR_CUDA);
   ctx->own_stream = true;
   ctx->max_tiles = (uint32_t)((max_records + ctx->tile - 1) / ctx->tile);
@@ -227,6 +231,7 @@ int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
   p.term_mask = ctx->term_mask;
   p.gen = ++ctx->gen;
   memcpy(p.lut, ctx->lut, sizeof p.lut);
+  memcpy(p.code, ctx->code, sizeof p.code);
 #ifdef NXS_TRACE
   if (!ctx->trace) cudaMalloc(&ctx->trace, 8 + 16 * (size_t)(1 << 20));
   cudaMemsetAsync(ctx->trace, 0, 8, ctx->stream);
@@ -423,7 +428,7 @@ extern "C" int nxs_classify_device_noalloc(int device, void *cuda_stream, uint16
   p.trace = nullptr;
   p.trace_cap = 0;
 #endif
-  nxs_build_lut(p.lut);
+  nxs_build_lut(p.lut, p.code);
   // The array still holds the previous call's descriptors and counters: the counters and every
   // descriptor this launch will read must start at zero.
   if (cudaMemsetAsync(dev->scratch, 0, kNoallocCounterBytes + sizeof(TileDesc) * (size_t)p.n_tiles, stream) != cudaSuccess) {

@@ -73,12 +73,17 @@ bool eq(const char *s, size_t len, const char *lit) { return strlen(lit) == len 
 } // namespace
 
 namespace nxs {
-void nxs_build_lut(uint8_t lut[128]) {
+void nxs_build_lut(uint8_t lut[128], uint8_t code[8]) {
   memset(lut, 0, 128);
-  // code = action | cause_tpl << 3 | msg_tpl << 5; cause template per action: :298, :325, :350, none for ToRunning
+  memset(code, 0, 8);
+  // cause template per action: :298, :325, :350, none for ToRunning
   static const uint8_t cause_of_action[5] = {0, 1, 2, 3, 0};
-  for (const SwitchArm &a : kSwitchArms)
-    lut[a.kind * 32 + a.reason] = (uint8_t)(a.action | cause_of_action[a.action] << 3 | a.msg_tpl << 5);
+  uint8_t arm = 0;
+  for (const SwitchArm &a : kSwitchArms) {
+    ++arm;
+    lut[a.kind * 32 + a.reason] = arm;
+    code[arm] = (uint8_t)(a.action | cause_of_action[a.action] << 3 | a.msg_tpl << 5);
+  }
 }
 } // namespace nxs
 

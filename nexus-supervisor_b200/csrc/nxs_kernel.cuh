@@ -3,95 +3,115 @@
 // One persistent grid makes a single pass over HBM: it classifies every record
 // (onEvent + superviseAction decision, services/supervisor.go:137-374) and folds
 // the records of each job into one row.  Each CTA is a warp-specialised pipeline
-// over a ring of shared-memory stages, driven by mbarriers only (no CTA-wide
-// barrier):
-//   producer warp  claims tile ids from a global counter and streams the five
-//                  input columns of a tile into a stage with 1-D bulk async
-//                  copies (TMA engine, SASS UBLKCP)
-//   worker warps   phase 1 as soon as a tile has landed.  Each warp owns a
-//                  contiguous range of the tile (TILE/8 records) and walks it 32
-//                  records at a time, lane per record: table lookups -> packed
-//                  verdict -> global; warp ballots -> bit masks kept in
-//                  registers; the lane holding the LAST record of a job folds the
-//                  job's masks into its row right away (codes of other lanes come
-//                  by shuffle, the job left open by the previous 32 records is
-//                  carried in registers) and parks key + packed row in shared
-//                  memory, compacted per range.
-//                  phase 2 once the tile's look-back is done: patch the one job
-//                  per range that began before the range, then copy the parked
-//                  rows to their final position in global memory
-//   scan warp      event loop: (a) as soon as phase 1 of a tile is complete,
-//                  publish its aggregate (job count + summary of the job left
-//                  open at its end) — this never waits on another CTA;
-//                  (b) poll predecessor descriptors (decoupled look-back) for
-//                  the oldest pending tile; when complete, publish the inclusive
-//                  descriptor and release phase 2
+// over a ring of shared-memory stages, driven by mbarriers only:
+//
+//   producer warp   claims tile ids from a global counter and streams the five
+//                   input columns of a tile into a stage with 1-D bulk async
+//                   copies (TMA engine, SASS UBLKCP)
+//   worker warps    (a) as soon as a tile has landed (checked between two tiles of
+//                   (b)) each warp compares the adjacent job
+//                   keys of its range, leaves the "last record of a job" bit masks
+//                   and its job count in the stage;
+//   counter warp    sums the eight range counts, publishes the tile's JOB COUNT,
+//                   polls predecessor tiles (decoupled look-back on counts only)
+//                   for the index of the tile's first job row and releases (b)
+//   worker warps    (b) each warp owns a contiguous range of the tile and walks it 32
+//                   records at a time, lane per record: table lookups -> packed
+//                   verdict -> global; warp ballots -> bit masks in registers; the
+//                   lane holding the last record of a job folds the job's masks
+//                   (codes of other lanes by shuffle, the job left open by the
+//                   previous 32 records carried in registers) and stores the
+//                   16-byte job row at its final position
+//   summary warp    after the workers: frees the stage, publishes the summary of
+//                   the job left open at the tile's end, and writes the few rows
+//                   the workers could not close — jobs that began before a
+//                   warp's range or before the tile (the latter after a second,
+//                   off-the-critical-path look-back on summaries)
+//
+// Splitting the look-back in two keeps the stage's residency short: the count is
+// known as soon as the keys have landed, so row positions are ready before the
+// expensive pass starts and no stage waits for another CTA's classification.
 // Scratch: TileDesc[n_tiles] (16 B each) + 3 counters.
 #pragma once
 #include "nxs_device.cuh"
 
 namespace nxs {
 
-constexpr int kWorkerWarps = 8;
+constexpr int kWorkerWarps = 16;
 constexpr int kWorkers = kWorkerWarps * 32;
 constexpr int kProducerWarp = kWorkerWarps;
-constexpr int kScanWarp = kWorkerWarps + 1;
-constexpr int kThreads = kWorkers + 64;
-constexpr int kStages = 3;
+constexpr int kCounterWarp = kWorkerWarps + 1;
+constexpr int kSummaryWarp = kWorkerWarps + 2;
+constexpr int kThreads = kWorkers + 96;
+constexpr int kPendingSlots = 4;                // tiles whose carried-in summary is still being looked up
 constexpr uint64_t kWatchdogNs = 8000000000ull; // a stuck wait traps instead of hanging the GPU
+
+template <int TILE> struct StagesFor {
+  static constexpr int value = TILE <= 2048 ? 4 : 2;
+};
 
 // What a worker warp leaves behind for its range of the tile.
 struct __align__(8) RangeInfo {
-  uint64_t suffix; // summary of the job still open at the end of the range (restricted to the range)
-  uint64_t unres;  // summary of the range's first job when it began before the range
-  uint32_t count;  // jobs ending in the range
+  uint64_t suffix;    // summary of the job still open at the end of the range (restricted to the range)
+  uint64_t unres;     // summary of the range's first job when it began before the range
+  uint64_t unres_key; // ... and its job key
   uint32_t flags;
-  uint32_t has_unres; // set by the lane that parked `unres`
-  uint32_t pad;
+  uint32_t has_unres; // set by the lane that left `unres`
 };
 enum : uint32_t { RANGE_CLOSED = 1u, RANGE_FIRST_IS_HEAD = 4u };
 
-// Parked row (phase 1 -> phase 2): Summ.f[0,16) | job already finished at its first record[16] |
-// winner index within the tile[17,..)
-constexpr uint32_t kParkedFin0 = 1u << 16;
-constexpr uint32_t kVerdictMask = 0x1FFFFu;
-
 template <int TILE> struct __align__(128) StageBuf {
   // keyx[1] = key of the record before the tile, keyx[2..TILE+1] = the tile's
-  // keys (16-byte aligned for the bulk copy), keyx[TILE+2] = key after the tile.
-  // Phase 1 compacts the keys of each range's job-ending records in place.
+  // keys (16-byte aligned for the bulk copy), keyx[TILE+2] = key after the tile
   uint64_t keyx[TILE + 4];
   uint16_t reason[TILE];
   uint8_t kind[TILE];
   uint8_t flags[TILE];
   uint8_t stage[TILE];
-  uint32_t packed[TILE]; // parked rows, compacted per range like the keys
+  uint32_t tailmask[TILE / 32]; // bit b: record 32*chunk + b is the last of its job
   RangeInfo range[kWorkerWarps];
+  uint32_t range_cnt[kWorkerWarps]; // jobs ending in each range
   uint32_t range_off[kWorkerWarps]; // jobs ending before each range, tile-local
-  uint64_t carry;                   // summary carried into the tile's first job
-  uint64_t local_summ;              // summary of the job left open at the tile's end
-  uint32_t local_count;             // jobs ending in the tile
   uint32_t tile_base;               // job rows before the tile
+  uint32_t first_is_head;           // the tile's first record begins a job
   int32_t tile;                     // tile id, -1 = end of work
+  uint32_t pad;
 };
 
 // Verdict table entry = packed verdict of the record plus the fold bits above it.
 constexpr uint32_t VT_HE = 1u << 17, VT_TERM = 1u << 18, VT_FAIL = 1u << 19, VT_ERR = 1u << 20;
+constexpr uint32_t kVerdictMask = 0x1FFFFu;
 
-struct Ctl {
-  uint64_t full[kStages];   // tile landed            (producer -> workers)
-  uint64_t p1done[kStages]; // phase 1 complete       (workers -> scan warp)
-  uint64_t lbdone[kStages]; // look-back complete     (scan warp -> workers)
-  uint64_t freeb[kStages];  // phase 2 complete       (workers -> producer)
-  uint32_t vt[1024];        // [gate class 0..3][code 0..255] -> verdict | fold bits
-  uint8_t lut[128];         // (kind, reason) -> code (action | cause_tpl << 3 | msg_tpl << 5)
-  uint16_t lut2[128];       // (flags & 7) | stage << 3 -> 256 * gate class (0 dropped, 1 no checkpoint, 2 finished, 3 apply)
+// A tile whose first job began in an earlier tile, parked by the summary warp until
+// the summary look-back has delivered what came before.
+struct PendingTile {
+  uint64_t unres[kWorkerWarps]; // per range: summary of the rows still to be closed
+  uint64_t key[kWorkerWarps];
+  uint32_t rowpos[kWorkerWarps];
+  uint32_t mask; // ranges with a row to close
+  uint32_t tile;
+  uint64_t local_summ; // open-job summary of the tile alone
+  uint32_t need_inc;   // that summary is not anchored: the inclusive one needs the carry
+  uint32_t pad;
+};
+
+template <int STAGES> struct Ctl {
+  uint64_t full[STAGES];       // tile landed              (producer -> workers)
+  uint64_t counted[STAGES];    // job boundaries marked    (workers -> counter warp)
+  uint64_t base_ready[STAGES]; // first row index known    (counter warp -> workers)
+  uint64_t p1done[STAGES];     // rows written             (workers -> summary warp)
+  uint64_t freeb[STAGES];      // stage reusable           (summary warp -> producer)
+  PendingTile pending[kPendingSlots];
+  uint32_t vt[32];   // [gate class 0..3][arm 0..7] -> verdict | fold bits
+  uint8_t lut[128];  // (kind, reason) -> switch arm 1..7, 0 = `default`
+  uint8_t lut2[128]; // (flags & 7) | stage << 3 -> 8 * gate class (0 dropped, 1 no checkpoint, 2 finished, 3 apply)
+  uint8_t code[8];   // arm -> action | cause_tpl << 3 | msg_tpl << 5
 };
 
 // Tile descriptor: two self-validating 64-bit words, each published with one
 // relaxed store, so no fence is needed on either side.
-//   c: count[0,32) | status[32,34) | generation[34,41)
-//   s: win_idx[0,32) | Summ.f[32,55) | status[55,57) | generation[57,64)
+//   c: job count[0,32) | status[32,34) | generation[34,41)      (counter warp)
+//   s: win_idx[0,32) | Summ.f[32,55) | status[55,57) | generation[57,64)   (summary warp)
 struct __align__(16) TileDesc {
   uint64_t c, s;
 };
@@ -131,7 +151,8 @@ struct ClassifyParams {
   uint32_t finished_mask;
   uint32_t term_mask; // bit a: new_stage_of(a) is a finished stage
   uint32_t gen;
-  uint8_t lut[128];
+  uint8_t lut[128]; // (kind, reason) -> arm
+  uint8_t code[8];  // arm -> code
 #ifdef NXS_TRACE
   unsigned long long *trace; // [0] = number of events, then (time, cta<<40 | event<<32 | tile) pairs
   uint32_t trace_cap;
@@ -139,26 +160,32 @@ struct ClassifyParams {
 };
 
 template <int TILE> constexpr size_t classify_smem_bytes() {
-  return sizeof(StageBuf<TILE>) * kStages + sizeof(Ctl);
+  return sizeof(StageBuf<TILE>) * StagesFor<TILE>::value + sizeof(Ctl<StagesFor<TILE>::value>);
 }
 
 #if defined(__CUDACC__)
 
-__device__ __forceinline__ void ld_desc(const TileDesc *d, uint64_t &c, uint64_t &s) {
-  asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(c), "=l"(s) : "l"(d) : "memory");
+#ifndef NXS_CLASSIFY_UNROLL
+#define NXS_CLASSIFY_UNROLL 2
+#endif
+constexpr int kClassifyUnroll = NXS_CLASSIFY_UNROLL;
+
+__device__ __forceinline__ uint64_t ld_desc_word(const uint64_t *p) {
+  uint64_t v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
 }
-__device__ __forceinline__ void st_desc(TileDesc *d, uint64_t c, uint64_t s) {
-  asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(d), "l"(c), "l"(s) : "memory");
+__device__ __forceinline__ void st_desc_word(uint64_t *p, uint64_t v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void named_barrier_workers() { asm volatile("bar.sync 1, %0;" ::"n"(kWorkers) : "memory"); }
 
 #ifdef NXS_TRACE
 // Debug build only: CTAs 0, 97 and 211 log pipeline events with the global timer.
-enum : uint32_t { EV_CLAIM = 1, EV_ISSUED, EV_P1_START, EV_P1_END, EV_AGG_START, EV_AGG_END, EV_LB_START, EV_LB_END,
-                  EV_P2_START, EV_P2_END, EV_LB_POLL };
+enum : uint32_t { EV_CLAIM = 1, EV_ISSUED, EV_COUNT_START, EV_COUNT_END, EV_LB_START, EV_LB_END, EV_P1_START,
+                  EV_P1_END, EV_SUM_START, EV_SUM_END, EV_LB_POLL, EV_SLB_END };
 __device__ __forceinline__ void trace_event(const ClassifyParams &p, uint32_t ev, uint32_t tile) {
   if (!p.trace || !(blockIdx.x == 0 || blockIdx.x == 97 || blockIdx.x == 211)) return;
   const unsigned long long i = atomicAdd(p.trace, 1ull);
@@ -188,13 +215,17 @@ struct Watchdog {
   __device__ __forceinline__ void reset() { t0 = 0; spins = 0; }
 };
 
+__device__ __forceinline__ Summ shfl_summ(Summ s, int src) {
+  return Summ{__shfl_sync(0xffffffffu, s.win_idx, src), __shfl_sync(0xffffffffu, s.f, src)};
+}
+
 // --------------------------------------------------------------------- producer
-template <int TILE>
-__device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl &ctl) {
+template <int TILE, int STAGES>
+__device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl) {
   uint32_t next = atomicAdd(p.counters, 1u);
   Watchdog wd;
   for (uint32_t k = 0;; ++k) {
-    const uint32_t s = k % kStages, use = k / kStages;
+    const uint32_t s = k % STAGES, use = k / STAGES;
     if (use > 0) {
       while (!mbar_try_wait(&ctl.freeb[s], (use - 1) & 1u, 20000u)) wd.tick(p.counters + 2);
       wd.reset();
@@ -234,69 +265,233 @@ __device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<
   }
 }
 
-// ---------------------------------------------------------------------- workers
-__device__ __forceinline__ Summ shfl_summ(Summ s, int src) {
-  return Summ{__shfl_sync(0xffffffffu, s.win_idx, src), __shfl_sync(0xffffffffu, s.f, src)};
-}
-__device__ __forceinline__ Summ shfl_down_summ(Summ s, int d) {
-  return Summ{__shfl_down_sync(0xffffffffu, s.win_idx, d), __shfl_down_sync(0xffffffffu, s.f, d)};
+// ------------------------------------------------------ job boundaries (workers)
+// One worker warp marks the job boundaries of its range of a landed tile: the "last
+// record of its job" masks and the number of jobs ending in the range.  Warp 0 also
+// notes whether the tile's first record begins a job.  A ragged (last) tile is read
+// from global memory here and copied into the stage for the classification pass.
+template <int TILE>
+__device__ __noinline__ void count_range(const ClassifyParams &p, StageBuf<TILE> &sb, uint32_t tile, uint32_t warp,
+                                         uint32_t lane) {
+  constexpr uint32_t RANGE = TILE / kWorkerWarps, CPW = RANGE / 32;
+  const uint32_t start = tile * TILE;
+  const uint32_t cnt = min((uint32_t)TILE, p.n - start);
+  const uint32_t r0 = warp * RANGE;
+  uint32_t jobs = 0;
+  if (cnt == (uint32_t)TILE) {
+    const bool last_tile = start + cnt == p.n;
+#pragma unroll
+    for (uint32_t j = 0; j < CPW; ++j) {
+      const uint32_t i = r0 + j * 32 + lane;
+      bool tail = sb.keyx[2 + i] != sb.keyx[3 + i];
+      if (last_tile && i == TILE - 1) tail = true;
+      const uint32_t T = __ballot_sync(0xffffffffu, tail);
+      if (lane == 0) sb.tailmask[r0 / 32 + j] = T;
+      jobs += __popc(T);
+    }
+    if (warp == 0 && lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(sb.keyx[2] != sb.keyx[1]);
+  } else { // ragged last tile (once per launch)
+    for (uint32_t j = 0; j < CPW; ++j) {
+      const uint32_t i = r0 + j * 32 + lane;
+      bool tail = false;
+      if (i < cnt) {
+        const uint64_t key = p.key[start + i];
+        tail = (i == cnt - 1) || key != p.key[start + i + 1];
+        sb.keyx[2 + i] = key;
+        sb.reason[i] = p.reason[start + i];
+        sb.kind[i] = p.kind[start + i];
+        sb.flags[i] = p.flags[start + i];
+        sb.stage[i] = p.stage[start + i];
+      }
+      const uint32_t T = __ballot_sync(0xffffffffu, tail);
+      if (lane == 0) sb.tailmask[r0 / 32 + j] = T;
+      jobs += __popc(T);
+    }
+    if (warp == 0 && lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(p.key[start] != p.key[start - 1]);
+  }
+  if (lane == 0) sb.range_cnt[warp] = jobs;
 }
 
-template <int TILE, bool FULL>
-__device__ __forceinline__ void phase1(const ClassifyParams &p, StageBuf<TILE> &sb, const Ctl &ctl, uint32_t tile,
-                                       uint32_t warp, uint32_t lane) {
+// What a worker warp remembers about the tiles it still has to mark.
+struct CountStream {
+  uint32_t s, par;
+  bool end;
+};
+// Marks every tile that has landed since the last call (usually none or one).
+template <int TILE, int STAGES>
+__device__ __forceinline__ void service_counts(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
+                                               CountStream &cs, uint32_t warp, uint32_t lane) {
+  while (!cs.end && __all_sync(0xffffffffu, mbar_test_wait(&ctl.full[cs.s], cs.par))) {
+    StageBuf<TILE> &sb = stages[cs.s];
+    const int32_t t = sb.tile;
+    if (t < 0) cs.end = true;
+    else count_range<TILE>(p, sb, (uint32_t)t, warp, lane);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&ctl.counted[cs.s]);
+    if (++cs.s == STAGES) cs.s = 0, cs.par ^= 1u;
+  }
+}
+
+// ----------------------------------------------------------------- counter warp
+struct CountLookback {
+  int pos;       // nearest predecessor tile of the next window
+  uint32_t excl; // job rows counted so far
+};
+constexpr int kCountWindows = 8;
+// One non-blocking step of the count look-back: kCountWindows x 32 predecessor count
+// words in one round trip (independent loads), consumed 32 at a time, nearest first.
+// A window is consumed only when every word it needs has been published.
+__device__ __forceinline__ bool count_lookback_poll(const ClassifyParams &p, CountLookback &st, uint32_t lane) {
+  uint64_t c[kCountWindows];
+#pragma unroll
+  for (int k = 0; k < kCountWindows; ++k) {
+    const int idx = st.pos - (int)lane - 32 * k;
+    c[k] = idx >= 0 ? ld_desc_word(&p.desc[idx].c) : 0ull;
+  }
+#pragma unroll
+  for (int k = 0; k < kCountWindows; ++k) {
+    const bool valid = st.pos - (int)lane >= 0;
+    const uint32_t cs = desc_c_status(c[k], p.gen);
+    const uint32_t m_valid = __ballot_sync(0xffffffffu, valid);
+    const uint32_t m_ok = __ballot_sync(0xffffffffu, valid && cs != DESC_INVALID);
+    const uint32_t m_inc = __ballot_sync(0xffffffffu, valid && cs == DESC_INC);
+    const uint32_t need = m_inc ? (2u << lo_bit(m_inc)) - 1u : m_valid;
+    if (need & ~m_ok) return false;
+    uint32_t contrib = ((need >> lane) & 1u) ? (uint32_t)c[k] : 0u;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, d);
+    st.excl += contrib;
+    if (m_inc) return true;
+    st.pos -= 32;
+  }
+  return false;
+}
+
+template <int TILE, int STAGES>
+__device__ __forceinline__ void counter_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
+                                             uint32_t lane) {
+  uint32_t kc = 0, sc = 0, parc = 0; // next tile to total: ordinal, stage, parity
+  uint32_t kb = 0, sbi = 0;          // next tile whose first row index is looked up
+  uint32_t totals[STAGES];           // job count of the tile in each stage
+  bool end = false, lb_active = false;
+  CountLookback st{0, 0u};
+  Watchdog wd;
+  while (true) {
+    // Publishing the count of a marked tile comes first: it never waits on another CTA and every
+    // later tile needs it.
+    if (!end && __all_sync(0xffffffffu, mbar_test_wait(&ctl.counted[sc], parc))) {
+      StageBuf<TILE> &sb = stages[sc];
+      const int32_t t = sb.tile;
+      if (t < 0) {
+        end = true;
+      } else {
+        if (lane == 0) NXS_TRACE_EVENT(p, EV_COUNT_START, (uint32_t)t);
+        const uint32_t mine = lane < (uint32_t)kWorkerWarps ? sb.range_cnt[lane] : 0u;
+        uint32_t incl = mine;
+#pragma unroll
+        for (int d = 1; d < kWorkerWarps; d <<= 1) {
+          const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+          if ((int)lane >= d) incl += o;
+        }
+        if (lane < (uint32_t)kWorkerWarps) sb.range_off[lane] = incl - mine;
+        const uint32_t total = __shfl_sync(0xffffffffu, incl, kWorkerWarps - 1);
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s)
+          if (s == (int)sc) totals[s] = total;
+        if (lane == 0) {
+          st_desc_word(&p.desc[t].c, desc_c(total, t == 0 ? DESC_INC : DESC_AGG, p.gen));
+          if (p.n_tiles == 1) *p.n_jobs = total;
+        }
+        if (lane == 0) NXS_TRACE_EVENT(p, EV_COUNT_END, (uint32_t)t);
+        ++kc;
+        if (++sc == STAGES) sc = 0, parc ^= 1u;
+      }
+      wd.reset();
+      continue;
+    }
+    if (kb < kc) { // look up the first row index of the oldest counted tile
+      StageBuf<TILE> &sb = stages[sbi];
+      const uint32_t tile = (uint32_t)sb.tile;
+      if (!lb_active) {
+        st.pos = (int)tile - 1;
+        st.excl = 0;
+        lb_active = true;
+        if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_START, tile);
+      }
+      if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_POLL, tile);
+      if (tile == 0 || count_lookback_poll(p, st, lane)) {
+        uint32_t total = 0;
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s)
+          if (s == (int)sbi) total = totals[s];
+        if (lane == 0) {
+          if (tile != 0) st_desc_word(&p.desc[tile].c, desc_c(st.excl + total, DESC_INC, p.gen));
+          if (tile == p.n_tiles - 1) *p.n_jobs = (uint64_t)st.excl + total;
+          sb.tile_base = st.excl;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&ctl.base_ready[sbi]);
+        if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_END, tile);
+        lb_active = false;
+        ++kb;
+        if (++sbi == STAGES) sbi = 0;
+        wd.reset();
+        continue;
+      }
+    } else if (end) {
+      if (lane == 0) mbar_arrive(&ctl.base_ready[sc]); // wake the workers on the end marker
+      break;
+    } else {
+      (void)__all_sync(0xffffffffu, mbar_try_wait(&ctl.counted[sc], parc, 2000u));
+    }
+    wd.tick(p.counters + 2);
+  }
+}
+
+// ---------------------------------------------------------------------- workers
+template <int TILE, bool FULL, int STAGES>
+__device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf<TILE> *stages, StageBuf<TILE> &sb,
+                                               Ctl<STAGES> &ctl, CountStream &cs, uint32_t tile, uint32_t warp,
+                                               uint32_t lane) {
   constexpr uint32_t RANGE = TILE / kWorkerWarps; // records per warp
   constexpr uint32_t CPW = RANGE / 32;            // 32-record chunks per warp
   const uint32_t start = tile * TILE;
   const uint32_t cnt = FULL ? (uint32_t)TILE : p.n - start;
-  if (!FULL) { // ragged tile: guarded loads by the worker warps, then a worker-only barrier
-    for (uint32_t i = warp * 32 + lane; i < cnt; i += kWorkers) {
-      sb.keyx[2 + i] = p.key[start + i];
-      sb.reason[i] = p.reason[start + i];
-      sb.kind[i] = p.kind[start + i];
-      sb.flags[i] = p.flags[start + i];
-      sb.stage[i] = p.stage[start + i];
-    }
-    if (warp == 0 && lane == 0 && start > 0) sb.keyx[1] = p.key[start - 1];
-    named_barrier_workers();
-  }
   const uint32_t r0 = warp * RANGE;
   if (!FULL && r0 >= cnt) { // nothing of the ragged tile falls in this range
-    if (lane == 0) sb.range[warp] = RangeInfo{summ_pack(summ_identity()), 0ull, 0u, 0u, 0u, 0u};
+    if (lane == 0) sb.range[warp] = RangeInfo{summ_pack(summ_identity()), 0ull, 0ull, 0u, 0u};
     return;
   }
-  const bool last_tile = start + cnt == p.n;
   const uint32_t gbase = p.record_base + start;
   const uint32_t le = (2u << lane) - 1u, lt = le >> 1;
+  nxs_job_row *rows = p.rows + sb.tile_base + sb.range_off[warp];
   // Does the first record of the range begin a job?  (warp-uniform)
-  uint32_t prev_bit = (r0 == 0 && start == 0) ? 1u : (uint32_t)(sb.keyx[2 + r0] != sb.keyx[1 + r0]);
+  uint32_t prev_bit = r0 == 0 ? sb.first_is_head : sb.tailmask[r0 / 32 - 1] >> 31;
   const uint32_t first_is_head = prev_bit;
   Summ ctx = summ_identity(); // the job left open by the records of this range seen so far
   uint32_t wcount = 0, closed = 0;
   if (lane == 0) sb.range[warp].has_unres = 0;
   __syncwarp();
 
-#pragma unroll
+#pragma unroll kClassifyUnroll
   for (uint32_t j = 0; j < CPW; ++j) {
+    if (j) service_counts<TILE, STAGES>(p, stages, ctl, cs, warp, lane); // a tile that just landed goes first
     const uint32_t i = r0 + j * 32 + lane;
     const bool valid = FULL || i < cnt;
+    const uint32_t T = sb.tailmask[r0 / 32 + j];
     uint32_t st = 0, vt = 0, code = 0;
     uint64_t key = 0;
-    bool tail = false;
     if (valid) {
       const uint32_t kind = sb.kind[i], reason = sb.reason[i], fl = sb.flags[i];
       st = sb.stage[i] & 15u;
       key = sb.keyx[2 + i];
-      const uint64_t nk = sb.keyx[3 + i];
-      tail = key != nk;
-      if (last_tile && i == cnt - 1) tail = true;
       // onEvent: guards (:155,:161,:218) and the (kind, reason) switch arms, then superviseAction's
-      // order: no checkpoint (:265) -> finished (:276) -> switch (:283).  All three are table lookups.
-      code = ctl.lut[min(kind, 3u) * 32u + (reason < 32u ? reason : 0u)];
-      vt = ctl.vt[ctl.lut2[(fl & 7u) | st << 3] + code];
+      // order: no checkpoint (:265) -> finished (:276) -> switch (:283).  All of it is table lookups.
+      const uint32_t arm = ctl.lut[min(kind, 3u) * 32u + (reason < 32u ? reason : 0u)];
+      code = ctl.code[arm];
+      vt = ctl.vt[ctl.lut2[(fl & 7u) | st << 3] + arm];
       __stcs(p.verdict + start + i, vt & kVerdictMask);
     }
-    const uint32_t T = __ballot_sync(0xffffffffu, tail);
     const uint32_t H = T << 1 | prev_bit; // bit b: record b of the chunk begins a job
     prev_bit = T >> 31;
     const uint32_t HE = ballot_bit(vt, VT_HE), TM = ballot_bit(vt, VT_TERM);
@@ -326,310 +521,263 @@ __device__ __forceinline__ void phase1(const ClassifyParams &p, StageBuf<TILE> &
     if (h_in) S.f |= st_head << F_S0_SHIFT | F_ANCHORED; // the job begins in this chunk
     else S = summ_combine(ctx, S);                        // it continues the job left open before the chunk
 
-    __syncwarp(); // every lane has read its keys: compaction may overwrite them now
-    if (tail) {
-      const uint32_t slot = r0 + wcount + __popc(T & lt);
-      sb.keyx[2 + slot] = key;
+    if ((T >> lane) & 1u) { // this record ends a job: close it and store its row
       if (S.f & F_ANCHORED) {
-        const uint32_t fin0 = (p.finished_mask >> ((S.f >> F_S0_SHIFT) & 15u)) & 1u;
-        sb.packed[slot] = (S.f & 0xFFFFu) | fin0 << 16 | (S.win_idx - gbase) << 17;
-      } else { // only the first job of a range can have begun before it
+        uint32_t verdict, winner;
+        summ_resolve(S, p.finished_mask, verdict, winner);
+        __stcs(reinterpret_cast<uint4 *>(rows + wcount + __popc(T & lt)),
+               make_uint4((uint32_t)key, (uint32_t)(key >> 32), verdict, winner));
+      } else { // only the first job of a range can have begun before it: left to the summary warp
         sb.range[warp].unres = summ_pack(S);
+        sb.range[warp].unres_key = key;
         sb.range[warp].has_unres = 1;
       }
     }
     wcount += __popc(T);
     if (FULL || r0 + j * 32 + 31 < cnt) closed = T >> 31;
-    else if (last_tile) closed = 1; // the ragged tile ends inside this chunk: its last record closes a job
+    else closed = 1; // the ragged (hence last) tile ends inside this chunk: its last record closes a job
     ctx = shfl_summ(S, 31);
   }
   __syncwarp();
   if (lane == 0) {
     sb.range[warp].suffix = summ_pack(ctx);
-    sb.range[warp].count = wcount;
     sb.range[warp].flags = (closed ? RANGE_CLOSED : 0u) | (first_is_head ? RANGE_FIRST_IS_HEAD : 0u);
   }
 }
 
-template <int TILE>
-__device__ __forceinline__ void phase2(const ClassifyParams &p, const StageBuf<TILE> &sb, uint32_t warp,
-                                       uint32_t lane) {
-  constexpr uint32_t RANGE = TILE / kWorkerWarps;
-  const uint32_t count = sb.range[warp].count;
-  if (count == 0) return;
-  const uint32_t r0 = warp * RANGE;
-  const uint32_t gbase = p.record_base + (uint32_t)sb.tile * TILE;
-  nxs_job_row *rows = p.rows + sb.tile_base + sb.range_off[warp];
-  uint32_t first = 0;
-  if (sb.range[warp].has_unres) { // the range's first job began before the range: gather what came before
-    if (lane == 0) {
-      Summ acc = summ_identity();
-      bool anchored = false;
-      for (int w = (int)warp - 1; w >= 0 && !anchored; --w) {
-        const Summ sfx = summ_unpack(sb.range[w].suffix);
-        acc = summ_combine(sfx, acc);
-        anchored = (sfx.f & F_ANCHORED) != 0;
-      }
-      if (!anchored) acc = summ_combine(summ_unpack(sb.carry), acc);
-      uint32_t verdict, winner;
-      summ_resolve(summ_combine(acc, summ_unpack(sb.range[warp].unres)), p.finished_mask, verdict, winner);
-      const uint64_t key = sb.keyx[2 + r0];
-      __stcs(reinterpret_cast<uint4 *>(rows), make_uint4((uint32_t)key, (uint32_t)(key >> 32), verdict, winner));
-    }
-    first = 1;
-  }
-  for (uint32_t j = first + lane; j < count; j += 32) {
-    const uint64_t key = sb.keyx[2 + r0 + j];
-    const uint32_t pk = sb.packed[r0 + j];
-    // close the job (summ_resolve on the parked fields)
-    const bool fin0 = (pk & kParkedFin0) != 0;
-    uint32_t v = fin0 ? (((pk & F_HAS_APP) ? F_SKIP : 0u) | (pk & F_ERR))
-                      : ((pk & F_VERDICT_MASK) | new_stage_of(pk & F_ALAST_MASK) << 3);
-    v |= (pk & F_ERR) >> 3;
-    const uint32_t winner = (!fin0 && (pk & F_HAS_WIN)) ? gbase + (pk >> 17) : NXS_NO_WINNER;
-    __stcs(reinterpret_cast<uint4 *>(rows + j), make_uint4((uint32_t)key, (uint32_t)(key >> 32), v, winner));
-  }
-}
-
-template <int TILE>
-__device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl &ctl,
+template <int TILE, int STAGES>
+__device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
                                             uint32_t warp, uint32_t lane) {
-  uint32_t k1 = 0, s1 = 0, par1 = 0; // next tile for phase 1: ordinal, stage, parity
-  uint32_t k2 = 0, s2 = 0, par2 = 0; // next tile for phase 2
-  bool end = false;
+  uint32_t s = 0, par = 0; // next tile to classify: stage, parity
+  CountStream cs{0u, 0u, false};
   Watchdog wd;
   while (true) {
-    // Phase 1 of a landed tile comes first (it feeds the aggregate every later tile waits for); a warp
-    // with nothing to fold sleeps on the barrier it needs next instead of polling.
-    bool landed = false;
-    if (!end) {
-      const bool p2_pending = k2 < k1;
-      landed = __all_sync(0xffffffffu, p2_pending ? mbar_test_wait(&ctl.full[s1], par1)
-                                                  : mbar_try_wait(&ctl.full[s1], par1, 2000u));
-    }
-    if (landed) {
-      StageBuf<TILE> &sb = stages[s1];
-      const int32_t t = sb.tile;
-      if (t < 0) {
-        end = true;
-      } else {
-        if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_START, (uint32_t)t);
-        if (p.n - (uint32_t)t * TILE >= (uint32_t)TILE) phase1<TILE, true>(p, sb, ctl, (uint32_t)t, warp, lane);
-        else phase1<TILE, false>(p, sb, ctl, (uint32_t)t, warp, lane);
-        if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_END, (uint32_t)t);
-        ++k1;
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&ctl.p1done[s1]);
-      if (++s1 == kStages) s1 = 0, par1 ^= 1u;
-      wd.reset();
+    service_counts<TILE, STAGES>(p, stages, ctl, cs, warp, lane);
+    // classify when the tile's first row index is known; otherwise sleep on whichever comes next
+    const bool ready = __all_sync(0xffffffffu, cs.end ? mbar_try_wait(&ctl.base_ready[s], par, 2000u)
+                                                      : mbar_test_wait(&ctl.base_ready[s], par));
+    if (!ready) {
+      if (!cs.end) (void)__all_sync(0xffffffffu, mbar_try_wait(&ctl.full[cs.s], cs.par, 500u));
+      wd.tick(p.counters + 2);
       continue;
     }
-    if (k2 < k1) {
-      if (__all_sync(0xffffffffu, mbar_try_wait(&ctl.lbdone[s2], par2, end ? 2000u : 300u))) {
-        if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P2_START, (uint32_t)stages[s2].tile);
-        phase2<TILE>(p, stages[s2], warp, lane);
-        if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P2_END, (uint32_t)stages[s2].tile);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&ctl.freeb[s2]);
-        ++k2;
-        if (++s2 == kStages) s2 = 0, par2 ^= 1u;
-        wd.reset();
-        continue;
-      }
-    } else if (end) {
-      break;
+    wd.reset();
+    StageBuf<TILE> &sb = stages[s];
+    const int32_t t = sb.tile;
+    if (t >= 0) {
+      if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_START, (uint32_t)t);
+      if (p.n - (uint32_t)t * TILE >= (uint32_t)TILE)
+        classify_range<TILE, true, STAGES>(p, stages, sb, ctl, cs, (uint32_t)t, warp, lane);
+      else
+        classify_range<TILE, false, STAGES>(p, stages, sb, ctl, cs, (uint32_t)t, warp, lane);
+      if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_END, (uint32_t)t);
     }
-    wd.tick(p.counters + 2);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&ctl.p1done[s]);
+    if (t < 0) break;
+    if (++s == STAGES) s = 0, par ^= 1u;
   }
 }
 
-// -------------------------------------------------------------------- scan warp
-// Tile-local job count, per-range row offsets and the summary of the job left
-// open at the end of the tile; publishes the tile's aggregate descriptor.
-template <int TILE>
-__device__ __forceinline__ void aggregate_tile(const ClassifyParams &p, StageBuf<TILE> &sb, uint32_t tile,
-                                               uint32_t lane) {
-  const uint32_t mine = lane < (uint32_t)kWorkerWarps ? sb.range[lane].count : 0u;
-  uint32_t incl = mine;
-#pragma unroll
-  for (int d = 1; d < kWorkerWarps; d <<= 1) {
-    const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
-    if ((int)lane >= d) incl += o;
-  }
-  if (lane < (uint32_t)kWorkerWarps) sb.range_off[lane] = incl - mine;
-  const uint32_t total = __shfl_sync(0xffffffffu, incl, kWorkerWarps - 1);
-  if (lane == 0) {
-    // the job open at the tile's end: walk the ranges from the right until one holds its first record
-    Summ T = summ_identity();
-    for (int w = kWorkerWarps - 1; w >= 0; --w) {
-      if (sb.range[w].flags & RANGE_CLOSED) { // (everything right of a closed range is empty)
-        T = Summ{0u, F_ANCHORED};             // nothing flows into the next tile
-        break;
-      }
-      T = summ_combine(summ_unpack(sb.range[w].suffix), T);
-      if (T.f & F_ANCHORED) break;
-    }
-    sb.local_count = total;
-    sb.local_summ = summ_pack(T);
-    if (tile == 0) {
-      st_desc(p.desc, desc_c(total, DESC_INC, p.gen), desc_s(T, DESC_INC, p.gen));
-      if (p.n_tiles == 1) *p.n_jobs = total;
-    } else {
-      st_desc(p.desc + tile, desc_c(total, DESC_AGG, p.gen), desc_s(T, DESC_AGG, p.gen));
-    }
-  }
-  __syncwarp();
-}
-
-struct LookbackState {
-  int pos;          // nearest predecessor tile of the next window
-  uint32_t excl;    // job rows counted so far
-  Summ carry;       // summary gathered so far (nearest tiles combined last)
-  bool count_done;  // an inclusive count has been reached
-  bool summ_done;   // an anchored summary has been reached (or none is needed)
+// ----------------------------------------------------------------- summary warp
+struct SummLookback {
+  int pos;
+  Summ carry;
 };
-
-// One non-blocking look-back step.  The warp reads kLookbackWindows x 32 predecessor descriptors
-// in one round trip (the loads are independent, so they cost one latency) and consumes them 32 at
-// a time, nearest first.  A window is consumed only when every descriptor it needs has been
-// published; otherwise the walk stops there and the next poll resumes from it.  Returns true when
-// both walks (job count, carried summary) are complete.
-// Why several windows per round trip: tiles are published at up to ~100 per microsecond, and a walk
-// that advanced only 32 tiles per L2 round trip could never catch up with the newest inclusive tile.
-constexpr int kLookbackWindows = 8;
-__device__ __forceinline__ bool lookback_poll(const ClassifyParams &p, LookbackState &st, uint32_t lane) {
-  uint64_t c[kLookbackWindows], s[kLookbackWindows];
+constexpr int kSummWindows = 2;
+// One non-blocking step of the summary look-back: walks predecessor summary words,
+// nearest first, until one is anchored (holds the first record of the job).
+__device__ __forceinline__ bool summ_lookback_poll(const ClassifyParams &p, SummLookback &st, uint32_t lane) {
+  uint64_t s[kSummWindows];
 #pragma unroll
-  for (int k = 0; k < kLookbackWindows; ++k) {
+  for (int k = 0; k < kSummWindows; ++k) {
     const int idx = st.pos - (int)lane - 32 * k;
-    c[k] = 0;
-    s[k] = 0;
-    if (idx >= 0) ld_desc(p.desc + idx, c[k], s[k]);
+    s[k] = idx >= 0 ? ld_desc_word(&p.desc[idx].s) : 0ull;
   }
 #pragma unroll
-  for (int k = 0; k < kLookbackWindows; ++k) {
+  for (int k = 0; k < kSummWindows; ++k) {
     const bool valid = st.pos - (int)lane >= 0;
-    const uint32_t cs = desc_c_status(c[k], p.gen), ss = desc_s_status(s[k], p.gen);
+    const uint32_t ss = desc_s_status(s[k], p.gen);
     const Summ mine = desc_s_summ(s[k]);
     const uint32_t m_valid = __ballot_sync(0xffffffffu, valid);
-    const uint32_t m_cok = __ballot_sync(0xffffffffu, valid && cs != DESC_INVALID);
-    const uint32_t m_cinc = __ballot_sync(0xffffffffu, valid && cs == DESC_INC);
-    const uint32_t m_sok = __ballot_sync(0xffffffffu, valid && ss != DESC_INVALID);
-    const uint32_t m_sanch = __ballot_sync(0xffffffffu, valid && ss != DESC_INVALID && (mine.f & F_ANCHORED));
-    const uint32_t need_c = st.count_done ? 0u : (m_cinc ? (2u << lo_bit(m_cinc)) - 1u : m_valid);
-    const uint32_t need_s = st.summ_done ? 0u : (m_sanch ? (2u << lo_bit(m_sanch)) - 1u : m_valid);
-    if ((need_c & ~m_cok) | (need_s & ~m_sok)) return false;
-    if (!st.count_done) {
-      uint32_t contrib = ((need_c >> lane) & 1u) ? (uint32_t)c[k] : 0u;
-#pragma unroll
-      for (int d = 16; d > 0; d >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, d);
-      st.excl += contrib;
-      st.count_done = m_cinc != 0;
-    }
-    if (!st.summ_done) {
-      const uint32_t upto = hi_bit(need_s);
-      for (uint32_t j = 0; j <= upto; ++j) st.carry = summ_combine(shfl_summ(mine, (int)j), st.carry);
-      st.summ_done = m_sanch != 0;
-    }
-    if (st.count_done && st.summ_done) return true;
+    const uint32_t m_ok = __ballot_sync(0xffffffffu, valid && ss != DESC_INVALID);
+    const uint32_t m_anch = __ballot_sync(0xffffffffu, valid && ss != DESC_INVALID && (mine.f & F_ANCHORED));
+    const uint32_t need = m_anch ? (2u << lo_bit(m_anch)) - 1u : m_valid;
+    if (need & ~m_ok) return false;
+    const uint32_t upto = hi_bit(need);
+    for (uint32_t j = 0; j <= upto; ++j) st.carry = summ_combine(shfl_summ(mine, (int)j), st.carry);
+    if (m_anch) return true;
     st.pos -= 32;
   }
   return false;
 }
 
-template <int TILE>
-__device__ __forceinline__ void scan_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl &ctl, uint32_t lane) {
-  uint32_t ka = 0, sa = 0, para = 0; // next tile to aggregate
-  uint32_t kl = 0, sl = 0;           // next tile to look back for
+template <int TILE, int STAGES>
+__device__ __forceinline__ void summary_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
+                                             uint32_t lane) {
+  uint32_t s = 0, par = 0;
+  uint32_t q_head = 0, q_tail = 0; // pending tiles: ring [q_head, q_tail)
   bool end = false, lb_active = false;
-  LookbackState st{0, 0u, summ_identity(), false, false};
+  SummLookback st{0, summ_identity()};
   Watchdog wd;
   while (true) {
-    // Aggregates first: publishing one never waits on another CTA, and every later tile needs it.
-    if (!end && __all_sync(0xffffffffu, mbar_test_wait(&ctl.p1done[sa], para))) {
-      StageBuf<TILE> &sb = stages[sa];
+    // A finished tile comes first (frees its stage, publishes its summary) unless the pending ring is full.
+    if (!end && q_tail - q_head < (uint32_t)kPendingSlots &&
+        __all_sync(0xffffffffu, mbar_test_wait(&ctl.p1done[s], par))) {
+      StageBuf<TILE> &sb = stages[s];
       const int32_t t = sb.tile;
       if (t < 0) {
         end = true;
-      } else {
-        if (lane == 0) NXS_TRACE_EVENT(p, EV_AGG_START, (uint32_t)t);
-        aggregate_tile<TILE>(p, sb, (uint32_t)t, lane);
-        if (lane == 0) NXS_TRACE_EVENT(p, EV_AGG_END, (uint32_t)t);
-        ++ka;
-        if (++sa == kStages) sa = 0, para ^= 1u;
+        wd.reset();
+        continue;
       }
+      const uint32_t tile = (uint32_t)t;
+      if (lane == 0) NXS_TRACE_EVENT(p, EV_SUM_START, tile);
+      // lanes 0..7 take over what the workers left for their range, then the stage is free
+      const bool mine = lane < (uint32_t)kWorkerWarps;
+      const Summ suffix = mine ? summ_unpack(sb.range[lane].suffix) : summ_identity();
+      const uint32_t flags = mine ? sb.range[lane].flags : 0u;
+      const bool has_unres = mine && sb.range[lane].has_unres;
+      const Summ unres = has_unres ? summ_unpack(sb.range[lane].unres) : summ_identity();
+      const uint64_t ukey = has_unres ? sb.range[lane].unres_key : 0ull;
+      const uint32_t rowpos = mine ? sb.tile_base + sb.range_off[lane] : 0u;
+      const bool first_is_head = sb.first_is_head != 0;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ctl.freeb[s]);
+      if (++s == STAGES) s = 0, par ^= 1u;
+
+      // Which ranges hold the first record of the job they leave open (or end on a job boundary)?
+      const uint32_t anch_mask = __ballot_sync(0xffffffffu, mine && (suffix.f & F_ANCHORED));
+      const uint32_t closed_mask = __ballot_sync(0xffffffffu, mine && (flags & RANGE_CLOSED));
+      // (1) the job open at the tile's end: the ranges from the last such range to the right
+      //     (usually just the last range)
+      Summ T = summ_identity();
+      {
+        const uint32_t stop = anch_mask | closed_mask;
+        const int k0 = stop ? (int)hi_bit(stop) : 0;
+        if ((closed_mask >> k0) & 1u) {
+          T = Summ{0u, F_ANCHORED}; // nothing flows into the next tile (everything right of k0 is empty)
+        } else {
+          for (int w = k0; w < kWorkerWarps; ++w) T = summ_combine(T, shfl_summ(suffix, w));
+        }
+      }
+      // (2) for every range whose first job began before it: what the earlier ranges of the tile add,
+      //     nearest first, until one holds the job's first record (usually the range next to it)
+      Summ acc = summ_identity();
+      {
+        bool need = has_unres && lane > 0;
+        for (int d = 1; d < kWorkerWarps && __any_sync(0xffffffffu, need); ++d) {
+          const Summ sw = Summ{__shfl_up_sync(0xffffffffu, suffix.win_idx, d), __shfl_up_sync(0xffffffffu, suffix.f, d)};
+          if (need) {
+            acc = summ_combine(sw, acc);
+            if ((sw.f & F_ANCHORED) || (int)lane == d) need = false;
+          }
+        }
+      }
+      // (3) rows whose job began inside the tile can be closed now; the others wait for the carry
+      bool waits = false;
+      if (has_unres) {
+        const Summ S = summ_combine(acc, unres);
+        if (S.f & F_ANCHORED) {
+          uint32_t verdict, winner;
+          summ_resolve(S, p.finished_mask, verdict, winner);
+          __stcs(reinterpret_cast<uint4 *>(p.rows + rowpos),
+                 make_uint4((uint32_t)ukey, (uint32_t)(ukey >> 32), verdict, winner));
+        } else {
+          waits = true;
+        }
+      }
+      const uint32_t wait_mask = __ballot_sync(0xffffffffu, waits);
+      const bool t_anchored = (T.f & F_ANCHORED) != 0;
+      if (tile == 0 || (first_is_head && wait_mask == 0)) {
+        // nothing flows in from earlier tiles: the tile's summary is already inclusive
+        if (lane == 0) st_desc_word(&p.desc[tile].s, desc_s(T, DESC_INC, p.gen));
+      } else {
+        // an anchored summary is already inclusive even while some rows of the tile still wait
+        if (lane == 0) st_desc_word(&p.desc[tile].s, desc_s(T, t_anchored ? DESC_INC : DESC_AGG, p.gen));
+        PendingTile &q = ctl.pending[q_tail % kPendingSlots];
+        if (waits) {
+          q.unres[lane] = summ_pack(summ_combine(acc, unres));
+          q.key[lane] = ukey;
+          q.rowpos[lane] = rowpos;
+        }
+        if (lane == 0) {
+          q.mask = wait_mask;
+          q.tile = tile;
+          q.local_summ = summ_pack(T);
+          q.need_inc = t_anchored ? 0u : 1u;
+        }
+        __syncwarp();
+        ++q_tail;
+      }
+      if (lane == 0) NXS_TRACE_EVENT(p, EV_SUM_END, tile);
       wd.reset();
       continue;
     }
-    if (kl < ka) { // a tile waits for its look-back: poll its predecessors (each poll is one L2 round trip)
-      StageBuf<TILE> &sb = stages[sl];
-      const uint32_t tile = (uint32_t)sb.tile;
+    if (q_head != q_tail) { // oldest pending tile: look up what earlier tiles carry into it
+      PendingTile &q = ctl.pending[q_head % kPendingSlots];
       if (!lb_active) {
-        st.pos = (int)tile - 1;
-        st.excl = 0;
+        st.pos = (int)q.tile - 1;
         st.carry = summ_identity();
-        st.count_done = tile == 0;
-        st.summ_done = tile == 0 || (sb.range[0].flags & RANGE_FIRST_IS_HEAD); // nothing to carry
         lb_active = true;
-        if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_START, tile);
       }
-      if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_POLL, tile);
-      if ((st.count_done && st.summ_done) || lookback_poll(p, st, lane)) {
-        if (lane == 0) {
-          const Summ T = summ_unpack(sb.local_summ);
-          const uint32_t total = sb.local_count;
-          if (tile != 0) {
-            const Summ I = (T.f & F_ANCHORED) ? T : summ_combine(st.carry, T);
-            st_desc(p.desc + tile, desc_c(st.excl + total, DESC_INC, p.gen), desc_s(I, DESC_INC, p.gen));
-            if (tile == p.n_tiles - 1) *p.n_jobs = (uint64_t)st.excl + total;
-          }
-          sb.tile_base = st.excl;
-          sb.carry = summ_pack(st.carry);
+      if (summ_lookback_poll(p, st, lane)) {
+        const uint32_t tile = q.tile;
+        if (lane == 0 && q.need_inc) // a tile with no job start of its own passes the carried summary on
+          st_desc_word(&p.desc[tile].s, desc_s(summ_combine(st.carry, summ_unpack(q.local_summ)), DESC_INC, p.gen));
+        if ((q.mask >> lane) & 1u) {
+          uint32_t verdict, winner;
+          summ_resolve(summ_combine(st.carry, summ_unpack(q.unres[lane])), p.finished_mask, verdict, winner);
+          const uint64_t key = q.key[lane];
+          __stcs(reinterpret_cast<uint4 *>(p.rows + q.rowpos[lane]),
+                 make_uint4((uint32_t)key, (uint32_t)(key >> 32), verdict, winner));
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(&ctl.lbdone[sl]);
-        if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_END, tile);
+        if (lane == 0) NXS_TRACE_EVENT(p, EV_SLB_END, tile);
         lb_active = false;
-        ++kl;
-        if (++sl == kStages) sl = 0;
+        ++q_head;
         wd.reset();
         continue;
       }
     } else if (end) {
       break;
-    } else { // nothing pending: sleep until the workers finish phase 1 of the next tile
-      (void)__all_sync(0xffffffffu, mbar_try_wait(&ctl.p1done[sa], para, 2000u));
+    } else {
+      (void)__all_sync(0xffffffffu, mbar_try_wait(&ctl.p1done[s], par, 2000u));
     }
     wd.tick(p.counters + 2);
   }
 }
 
 template <int TILE>
-__global__ void __launch_bounds__(kThreads, 2) classify_kernel(const __grid_constant__ ClassifyParams p) {
+__global__ void __launch_bounds__(kThreads, TILE <= 2048 ? 2 : 1) classify_kernel(const __grid_constant__ ClassifyParams p) {
+  constexpr int STAGES = StagesFor<TILE>::value;
   // (no manual re-alignment: keeping the pointer derived from the array keeps it in the shared
   // address space, so accesses compile to LDS/STS rather than generic loads)
   extern __shared__ __align__(128) uint8_t smem_raw[];
   StageBuf<TILE> *stages = reinterpret_cast<StageBuf<TILE> *>(smem_raw);
-  Ctl &ctl = *reinterpret_cast<Ctl *>(smem_raw + sizeof(StageBuf<TILE>) * kStages);
+  Ctl<STAGES> &ctl = *reinterpret_cast<Ctl<STAGES> *>(smem_raw + sizeof(StageBuf<TILE>) * STAGES);
   const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   if (tid == 0) {
-    for (int s = 0; s < kStages; ++s) {
+    for (int s = 0; s < STAGES; ++s) {
       mbar_init(&ctl.full[s], 2);
+      mbar_init(&ctl.counted[s], kWorkerWarps);
+      mbar_init(&ctl.base_ready[s], 1);
       mbar_init(&ctl.p1done[s], kWorkerWarps);
-      mbar_init(&ctl.lbdone[s], 1);
-      mbar_init(&ctl.freeb[s], kWorkerWarps);
+      mbar_init(&ctl.freeb[s], 1);
     }
     mbar_fence_init();
   }
   if (tid < 128) {
     ctl.lut[tid] = p.lut[tid];
     const uint32_t fl = tid & 7u, st = tid >> 3;
-    ctl.lut2[tid] = (uint16_t)(256u * ((fl & 3u) != 3u ? 0u : !(fl & NXS_FLAG_CHECKPOINT) ? 1u : ((p.finished_mask >> st) & 1u) ? 2u : 3u));
+    ctl.lut2[tid] =
+        (uint8_t)(8u * ((fl & 3u) != 3u ? 0u : !(fl & NXS_FLAG_CHECKPOINT) ? 1u : ((p.finished_mask >> st) & 1u) ? 2u : 3u));
   }
-  for (uint32_t e = tid; e < 1024; e += kThreads) {
-    const uint32_t g = e >> 8, code = e & 255u, a = code & 7u, msg = code >> 5;
+  if (tid < 8) ctl.code[tid] = p.code[tid];
+  if (tid >= 128 && tid < 160) {
+    const uint32_t e = tid - 128, g = e >> 3, arm = e & 7u;
+    const uint32_t code = p.code[arm], a = code & 7u, msg = code >> 5;
     uint32_t v = 0;
     if (g != 0 && a >= 1 && a <= 4) {
       const uint32_t fold = VT_HE | (((p.term_mask >> a) & 1u) ? VT_TERM : 0u) | (a != NXS_ACTION_RUNNING ? VT_FAIL : 0u);
@@ -641,10 +789,11 @@ __global__ void __launch_bounds__(kThreads, 2) classify_kernel(const __grid_cons
   }
   __syncthreads(); // the only CTA-wide barrier
 
-  if (warp < (uint32_t)kWorkerWarps) worker_loop<TILE>(p, stages, ctl, warp, lane);
+  if (warp < (uint32_t)kWorkerWarps) worker_loop<TILE, STAGES>(p, stages, ctl, warp, lane);
   else if (warp == (uint32_t)kProducerWarp) {
-    if (lane == 0) producer_loop<TILE>(p, stages, ctl);
-  } else scan_loop<TILE>(p, stages, ctl, lane);
+    if (lane == 0) producer_loop<TILE, STAGES>(p, stages, ctl);
+  } else if (warp == (uint32_t)kCounterWarp) counter_loop<TILE, STAGES>(p, stages, ctl, lane);
+  else summary_loop<TILE, STAGES>(p, stages, ctl, lane);
 }
 
 #endif // __CUDACC__

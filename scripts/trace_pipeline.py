@@ -16,8 +16,8 @@ from nexus_supervisor_b200 import _abi  # noqa: E402
 _abi.LIB_PATH = os.path.join(ROOT, "nexus-supervisor_b200", "lib", "libnxs_classify_trace.so")
 import torch  # noqa: E402
 
-EV = {1: "claim", 2: "issued", 3: "p1_start", 4: "p1_end", 5: "agg_start", 6: "agg_end", 7: "lb_start", 8: "lb_end",
-      9: "p2_start", 10: "p2_end", 11: "lb_poll"}
+EV = {1: "claim", 2: "issued", 3: "count_start", 4: "count_end", 5: "lb_start", 6: "lb_end", 7: "p1_start",
+      8: "p1_end", 9: "sum_start", 10: "sum_end", 11: "lb_poll", 12: "slb_end"}
 
 
 def main():
@@ -55,23 +55,25 @@ def main():
     print(f"{cnt} events, span {(int(ev[:, 0].max()) - t0) / 1e3:.1f} us")
     for cta in sorted({k[0] for k in per}):
         tiles = sorted(k[1] for k in per if k[0] == cta)
-        print(f"--- CTA {cta}: {len(tiles)} tiles; times in us relative to kernel start; durations in ns")
-        print(" tile    claim  | load  wait  P1   gap  AGG  gap  LB(polls)  gap  P2 | claim->P2end")
-        agg = {k: [] for k in ("load", "w1", "p1", "g1", "agg", "g2", "lb", "g3", "p2", "tot", "polls")}
+        print(f"--- CTA {cta}: {len(tiles)} tiles; claim in us from kernel start; durations in ns")
+        print(" tile    claim  | issue  land+wait count  gap   LB(polls)  wait   P1    gap  SUM | claim->stage free")
+        cols = ("issue", "land", "count", "g1", "lb", "w2", "p1", "g2", "sum", "hold", "polls")
+        agg = {k: [] for k in cols}
         for i, tile in enumerate(tiles):
             d = per[(cta, tile)]
-            need = ("claim", "issued", "p1_start", "p1_end", "agg_start", "agg_end", "lb_start", "lb_end", "p2_start", "p2_end")
+            need = ("claim", "issued", "count_start", "count_end", "lb_start", "lb_end", "p1_start", "p1_end",
+                    "sum_start", "sum_end")
             if not all(k in d for k in need):
                 continue
-            vals = dict(load=d["issued"] - d["claim"], w1=d["p1_start"] - d["issued"], p1=d["p1_end"] - d["p1_start"],
-                        g1=d["agg_start"] - d["p1_end"], agg=d["agg_end"] - d["agg_start"], g2=d["lb_start"] - d["agg_end"],
-                        lb=d["lb_end"] - d["lb_start"], g3=d["p2_start"] - d["lb_end"], p2=d["p2_end"] - d["p2_start"],
-                        tot=d["p2_end"] - d["claim"], polls=polls.get((cta, tile), 0))
+            vals = dict(issue=d["issued"] - d["claim"], land=d["count_start"] - d["issued"],
+                        count=d["count_end"] - d["count_start"], g1=d["lb_start"] - d["count_end"],
+                        lb=d["lb_end"] - d["lb_start"], w2=d["p1_start"] - d["lb_end"], p1=d["p1_end"] - d["p1_start"],
+                        g2=d["sum_start"] - d["p1_end"], sum=d["sum_end"] - d["sum_start"],
+                        hold=d["sum_start"] - d["claim"], polls=polls.get((cta, tile), 0))
             for k, v in vals.items():
                 agg[k].append(v)
             if i < 12 or i % 40 == 0:
-                print(f"{tile:6d} {d['claim'] / 1e3:8.1f} | {vals['load']:5d} {vals['w1']:5d} {vals['p1']:5d} {vals['g1']:5d} "
-                      f"{vals['agg']:4d} {vals['g2']:5d} {vals['lb']:5d}({vals['polls']:2d}) {vals['g3']:5d} {vals['p2']:4d} | {vals['tot']:6d}")
+                print(f"{tile:6d} {d['claim'] / 1e3:8.1f} | " + " ".join(f"{vals[k]:6d}" for k in cols))
         print(" median: " + "  ".join(f"{k}={int(np.median(v))}" for k, v in agg.items() if v))
         print(" mean:   " + "  ".join(f"{k}={int(np.mean(v))}" for k, v in agg.items() if v))
         if len(tiles) > 1:

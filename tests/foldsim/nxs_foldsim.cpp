@@ -27,8 +27,8 @@ extern "C" int nxs_foldsim(const uint8_t *kind, const uint16_t *reason, const ui
                            const uint64_t *key, uint64_t n, uint16_t finished_mask, uint32_t tile_records,
                            uint64_t lookback_seed, uint32_t *verdict, nxs_job_row *rows, uint64_t *n_jobs) {
   if (tile_records == 0 || tile_records % 32) return -1;
-  uint8_t lut[128];
-  nxs_build_lut(lut);
+  uint8_t lut[128], code_of_arm[8];
+  nxs_build_lut(lut, code_of_arm);
   uint32_t term_mask = 0;
   for (uint32_t a = 1; a <= 4; ++a)
     if ((finished_mask >> new_stage_of(a)) & 1u) term_mask |= 1u << a;
@@ -56,7 +56,7 @@ extern "C" int nxs_foldsim(const uint8_t *kind, const uint16_t *reason, const ui
         const uint32_t fl = flags[g], st = stage[g] & 15u;
         const uint32_t k = kind[g] < 3 ? kind[g] : 3u;
         const uint32_t idx = k * 32u + (reason[g] < 32u ? reason[g] : 0u);
-        const uint32_t cd = ((fl & 3u) == 3u) ? lut[idx] : 0u;
+        const uint32_t cd = ((fl & 3u) == 3u) ? code_of_arm[lut[idx]] : 0u;
         const uint32_t a = cd & 7u;
         const bool exists = (fl & NXS_FLAG_CHECKPOINT) != 0;
         const bool finished = (finished_mask >> st) & 1u;
