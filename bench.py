@@ -292,7 +292,7 @@ def main():
         e2e = {"value": n_all * args.e2e_steps / float(te[0]), "unit": UNIT, "h2d_bytes_per_step": int(13 * n),
                "d2h_bytes_per_step": int(4 * n + 16 * n_jobs + 8), "steps": args.e2e_steps,
                "ms_per_step": float(te[0]) / args.e2e_steps * 1e3,
-               "api": "nxs_classify (host pointers, pinned): H2D 5 columns + kernel + D2H verdicts and job rows"}
+               "api": "nxs_classify (host pointers, pinned): 8M-record slices, H2D of the 5 columns, kernel and D2H of verdicts + job rows overlapped on 3 streams"}
         for p in keep:
             nx._abi.load().nxs_free_host(p)
 

@@ -28,13 +28,17 @@ struct nxs_ctx {
   uint64_t launches = 0;
   uint8_t lut[128];
   uint8_t code[8];
-  // staging for the host-pointer entry point (allocated on first use)
-  uint64_t staged_records = 0;
-  uint8_t *d_in = nullptr;
-  uint32_t *d_verdict = nullptr;
-  nxs_job_row *d_rows = nullptr;
-  uint64_t *d_njobs = nullptr;
-  uint64_t *h_njobs = nullptr; // pinned
+  // staging for the host-pointer entry point (allocated on first use): two buffer sets, so the
+  // upload of one slice overlaps the classification and the download of the previous one
+  uint64_t staged_records = 0; // capacity of ONE set, in records
+  uint8_t *d_in[2] = {nullptr, nullptr};
+  uint32_t *d_verdict[2] = {nullptr, nullptr};
+  nxs_job_row *d_rows[2] = {nullptr, nullptr};
+  uint64_t *d_njobs = nullptr; // 2 counters
+  uint64_t *h_njobs = nullptr; // pinned, 2 counters
+  cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+  cudaEvent_t e_h2d[2] = {nullptr, nullptr}, e_kernel[2] = {nullptr, nullptr}, e_count[2] = {nullptr, nullptr},
+              e_d2h[2] = {nullptr, nullptr};
   char err[256] = {0};
 #ifdef NXS_TRACE
   unsigned long long *trace = nullptr;
@@ -146,8 +150,8 @@ int nxs_create(int device, uint64_t max_records, uint16_t finished_mask, nxs_ctx
   if (cudaMalloc(&ctx->counters, 64) != cudaSuccess) return bail(NXS_ERR_NOMEM);
   if (cudaMemset(ctx->desc, 0, sizeof(TileDesc) * (size_t)ctx->max_tiles) != cudaSuccess) return bail(NXS_ERR_CUDA);
   if (cudaMemset(ctx->counters, 0, 64) != cudaSuccess) return bail(NXS_ERR_CUDA);
-  if (cudaMalloc(&ctx->d_njobs, 8) != cudaSuccess) return bail(NXS_ERR_NOMEM);
-  if (cudaMallocHost(&ctx->h_njobs, 8) != cudaSuccess) return bail(NXS_ERR_NOMEM);
+  if (cudaMalloc(&ctx->d_njobs, 16) != cudaSuccess) return bail(NXS_ERR_NOMEM);
+  if (cudaMallocHost(&ctx->h_njobs, 16) != cudaSuccess) return bail(NXS_ERR_NOMEM);
   *out = ctx;
   return NXS_OK;
 }
@@ -161,9 +165,17 @@ void nxs_destroy(nxs_ctx *ctx) {
   }
   cudaFree(ctx->desc);
   cudaFree(ctx->counters);
-  cudaFree(ctx->d_in);
-  cudaFree(ctx->d_verdict);
-  cudaFree(ctx->d_rows);
+  for (int b = 0; b < 2; ++b) {
+    cudaFree(ctx->d_in[b]);
+    cudaFree(ctx->d_verdict[b]);
+    cudaFree(ctx->d_rows[b]);
+    if (ctx->e_h2d[b]) cudaEventDestroy(ctx->e_h2d[b]);
+    if (ctx->e_kernel[b]) cudaEventDestroy(ctx->e_kernel[b]);
+    if (ctx->e_count[b]) cudaEventDestroy(ctx->e_count[b]);
+    if (ctx->e_d2h[b]) cudaEventDestroy(ctx->e_d2h[b]);
+  }
+  if (ctx->s_h2d) cudaStreamDestroy(ctx->s_h2d);
+  if (ctx->s_d2h) cudaStreamDestroy(ctx->s_d2h);
   cudaFree(ctx->d_njobs);
   if (ctx->h_njobs) cudaFreeHost(ctx->h_njobs);
   cudaGetLastError();
@@ -189,7 +201,15 @@ int nxs_sync(nxs_ctx *ctx) {
 
 uint64_t nxs_launch_count(const nxs_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
+static int launch_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out, uint32_t record_base);
+
 int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
+  return launch_classify(ctx, in, out, 0);
+}
+
+// Validates device pointers and enqueues one classification launch on the ctx stream.
+// record_base is added to every winner_idx (used when a batch is processed in slices).
+static int launch_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out, uint32_t record_base) {
   if (!ctx || !in || !out) return NXS_ERR_ARG;
   if (!out->n_jobs) return fail_arg(ctx, "out->n_jobs is null");
   if (in->n > ctx->max_records) {
@@ -226,7 +246,7 @@ int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
   p.counters = ctx->counters;
   p.n = (uint32_t)in->n;
   p.n_tiles = (uint32_t)((in->n + ctx->tile - 1) / ctx->tile);
-  p.record_base = 0;
+  p.record_base = record_base;
   p.finished_mask = ctx->finished_mask;
   p.term_mask = ctx->term_mask;
   p.gen = ++ctx->gen;
@@ -248,23 +268,47 @@ int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
   return rc;
 }
 
-static int ensure_staging(nxs_ctx *ctx, uint64_t n) {
-  if (n <= ctx->staged_records) return NXS_OK;
-  cudaFree(ctx->d_in);
-  cudaFree(ctx->d_verdict);
-  cudaFree(ctx->d_rows);
-  ctx->d_in = nullptr;
-  ctx->d_verdict = nullptr;
-  ctx->d_rows = nullptr;
+// Records per slice of the host-pointer path.  Large enough that a launch is far from
+// launch-bound (thousands of tiles), small enough that upload, classification and download of
+// neighbouring slices overlap well.
+static const uint64_t kHostSliceRecords = 8u << 20;
+
+static int ensure_staging(nxs_ctx *ctx, uint64_t slice) {
+  if (!ctx->s_h2d) {
+    if (cudaStreamCreateWithFlags(&ctx->s_h2d, cudaStreamNonBlocking) != cudaSuccess) return NXS_ERR_CUDA;
+    if (cudaStreamCreateWithFlags(&ctx->s_d2h, cudaStreamNonBlocking) != cudaSuccess) return NXS_ERR_CUDA;
+    for (int b = 0; b < 2; ++b) {
+      if (cudaEventCreateWithFlags(&ctx->e_h2d[b], cudaEventDisableTiming) != cudaSuccess ||
+          cudaEventCreateWithFlags(&ctx->e_kernel[b], cudaEventDisableTiming) != cudaSuccess ||
+          cudaEventCreateWithFlags(&ctx->e_count[b], cudaEventDisableTiming) != cudaSuccess ||
+          cudaEventCreateWithFlags(&ctx->e_d2h[b], cudaEventDisableTiming) != cudaSuccess)
+        return NXS_ERR_CUDA;
+    }
+  }
+  if (slice <= ctx->staged_records) return NXS_OK;
+  const uint64_t cap = (slice + 1023) & ~1023ull; // keeps every column 16-byte aligned
+  for (int b = 0; b < 2; ++b) {
+    cudaFree(ctx->d_in[b]);
+    cudaFree(ctx->d_verdict[b]);
+    cudaFree(ctx->d_rows[b]);
+    ctx->d_in[b] = nullptr;
+    ctx->d_verdict[b] = nullptr;
+    ctx->d_rows[b] = nullptr;
+  }
   ctx->staged_records = 0;
-  const uint64_t cap = (n + 1023) & ~1023ull; // keeps every column 16-byte aligned
-  if (cudaMalloc(&ctx->d_in, cap * 13) != cudaSuccess) return NXS_ERR_NOMEM;
-  if (cudaMalloc(&ctx->d_verdict, cap * 4) != cudaSuccess) return NXS_ERR_NOMEM;
-  if (cudaMalloc(&ctx->d_rows, cap * sizeof(nxs_job_row)) != cudaSuccess) return NXS_ERR_NOMEM;
+  for (int b = 0; b < 2; ++b) {
+    if (cudaMalloc(&ctx->d_in[b], cap * 13) != cudaSuccess) return NXS_ERR_NOMEM;
+    if (cudaMalloc(&ctx->d_verdict[b], cap * 4) != cudaSuccess) return NXS_ERR_NOMEM;
+    if (cudaMalloc(&ctx->d_rows[b], cap * sizeof(nxs_job_row)) != cudaSuccess) return NXS_ERR_NOMEM;
+  }
   ctx->staged_records = cap;
   return NXS_OK;
 }
 
+// Host-pointer entry point.  The batch is cut into slices on job boundaries; slice k+1 is uploaded
+// (copy stream 1) while slice k is classified (ctx stream) and slice k-1 is downloaded (copy stream
+// 2), with two device buffer sets.  Job rows of consecutive slices are appended in the caller's
+// buffer, so a slice's rows are downloaded once the job count of the previous one is known.
 int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
   if (!ctx || !in || !out) return NXS_ERR_ARG;
   if (!out->n_jobs) return fail_arg(ctx, "out->n_jobs is null");
@@ -277,39 +321,99 @@ int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
       !out->job_rows)
     return fail_arg(ctx, "null column pointer");
   NXS_CUDA(ctx, cudaSetDevice(ctx->device));
-  int rc = ensure_staging(ctx, in->n);
+  const uint64_t n = in->n;
+  // A slice may grow past kHostSliceRecords to reach the end of its last job; leave room for that.
+  const uint64_t slice_cap = n <= kHostSliceRecords ? n : kHostSliceRecords + (kHostSliceRecords >> 3);
+  int rc = ensure_staging(ctx, slice_cap);
   if (rc != NXS_OK) {
     cudaGetLastError();
-    snprintf(ctx->err, sizeof ctx->err, "cannot allocate device staging for %llu records",
-             (unsigned long long)in->n);
+    snprintf(ctx->err, sizeof ctx->err, "cannot set up device staging for slices of %llu records",
+             (unsigned long long)slice_cap);
     return rc;
   }
-  const uint64_t n = in->n, cap = ctx->staged_records;
-  uint8_t *base = ctx->d_in;
-  uint64_t *d_key = reinterpret_cast<uint64_t *>(base);
-  uint16_t *d_reason = reinterpret_cast<uint16_t *>(base + cap * 8);
-  uint8_t *d_kind = base + cap * 10, *d_flags = base + cap * 11, *d_stage = base + cap * 12;
-  cudaStream_t st = ctx->stream;
-  NXS_CUDA(ctx, cudaMemcpyAsync(d_key, in->job_key, n * 8, cudaMemcpyHostToDevice, st));
-  NXS_CUDA(ctx, cudaMemcpyAsync(d_reason, in->reason_id, n * 2, cudaMemcpyHostToDevice, st));
-  NXS_CUDA(ctx, cudaMemcpyAsync(d_kind, in->kind, n, cudaMemcpyHostToDevice, st));
-  NXS_CUDA(ctx, cudaMemcpyAsync(d_flags, in->flags, n, cudaMemcpyHostToDevice, st));
-  NXS_CUDA(ctx, cudaMemcpyAsync(d_stage, in->cur_stage, n, cudaMemcpyHostToDevice, st));
-  nxs_batch d_in{d_kind, d_reason, d_flags, d_stage, d_key, n};
-  nxs_out d_out{ctx->d_verdict, ctx->d_rows, ctx->d_njobs};
-  rc = nxs_classify_device(ctx, &d_in, &d_out);
-  if (rc != NXS_OK) return rc;
-  NXS_CUDA(ctx, cudaMemcpyAsync(ctx->h_njobs, ctx->d_njobs, 8, cudaMemcpyDeviceToHost, st));
-  NXS_CUDA(ctx, cudaMemcpyAsync(out->verdict, ctx->d_verdict, n * 4, cudaMemcpyDeviceToHost, st));
-  NXS_CUDA(ctx, cudaStreamSynchronize(st));
-  const uint64_t n_jobs = *ctx->h_njobs;
-  if (n_jobs > n) {
-    snprintf(ctx->err, sizeof ctx->err, "internal error: n_jobs=%llu > n", (unsigned long long)n_jobs);
-    return NXS_ERR_CUDA;
+  const uint64_t cap = ctx->staged_records;
+  cudaStream_t s_comp = ctx->stream;
+  // everything enqueued earlier on the ctx stream must be done before the copy streams touch the staging
+  NXS_CUDA(ctx, cudaStreamSynchronize(s_comp));
+
+  uint64_t lo = 0, rows_done = 0;
+  uint64_t pend_lo[2] = {0, 0}, pend_n[2] = {0, 0}; // slices whose rows are still to be downloaded
+  bool pending[2] = {false, false};
+  auto finish_slice = [&](int b) -> int { // job count is (about to be) on the host: download the rows
+    NXS_CUDA(ctx, cudaEventSynchronize(ctx->e_count[b]));
+    const uint64_t jobs = ctx->h_njobs[b];
+    if (jobs > pend_n[b]) {
+      snprintf(ctx->err, sizeof ctx->err, "internal error: %llu jobs in a slice of %llu records",
+               (unsigned long long)jobs, (unsigned long long)pend_n[b]);
+      return NXS_ERR_CUDA;
+    }
+    NXS_CUDA(ctx, cudaMemcpyAsync(out->job_rows + rows_done, ctx->d_rows[b], jobs * sizeof(nxs_job_row),
+                                  cudaMemcpyDeviceToHost, ctx->s_d2h));
+    NXS_CUDA(ctx, cudaEventRecord(ctx->e_d2h[b], ctx->s_d2h));
+    rows_done += jobs;
+    pending[b] = false;
+    return NXS_OK;
+  };
+
+  for (int k = 0; lo < n; ++k) {
+    const int b = k & 1;
+    uint64_t hi = n - lo <= slice_cap ? n : lo + kHostSliceRecords;
+    while (hi < n && in->job_key[hi] == in->job_key[hi - 1] && hi - lo < cap) ++hi; // cut on a job boundary
+    if (hi < n && in->job_key[hi] == in->job_key[hi - 1]) {
+      snprintf(ctx->err, sizeof ctx->err, "a single job spans more than %llu records: pass the batch to "
+               "nxs_classify_device instead", (unsigned long long)(cap - kHostSliceRecords));
+      return NXS_ERR_CAPACITY;
+    }
+    const uint64_t m = hi - lo;
+    if (pending[b]) { // buffer set b still holds the slice before last: get its rows out first
+      rc = finish_slice(b);
+      if (rc != NXS_OK) return rc;
+    }
+    uint8_t *base = ctx->d_in[b];
+    uint64_t *d_key = reinterpret_cast<uint64_t *>(base);
+    uint16_t *d_reason = reinterpret_cast<uint16_t *>(base + cap * 8);
+    uint8_t *d_kind = base + cap * 10, *d_flags = base + cap * 11, *d_stage = base + cap * 12;
+    // upload (after the previous user of this buffer set has been fully downloaded)
+    NXS_CUDA(ctx, cudaStreamWaitEvent(ctx->s_h2d, ctx->e_d2h[b], 0));
+    NXS_CUDA(ctx, cudaMemcpyAsync(d_key, in->job_key + lo, m * 8, cudaMemcpyHostToDevice, ctx->s_h2d));
+    NXS_CUDA(ctx, cudaMemcpyAsync(d_reason, in->reason_id + lo, m * 2, cudaMemcpyHostToDevice, ctx->s_h2d));
+    NXS_CUDA(ctx, cudaMemcpyAsync(d_kind, in->kind + lo, m, cudaMemcpyHostToDevice, ctx->s_h2d));
+    NXS_CUDA(ctx, cudaMemcpyAsync(d_flags, in->flags + lo, m, cudaMemcpyHostToDevice, ctx->s_h2d));
+    NXS_CUDA(ctx, cudaMemcpyAsync(d_stage, in->cur_stage + lo, m, cudaMemcpyHostToDevice, ctx->s_h2d));
+    NXS_CUDA(ctx, cudaEventRecord(ctx->e_h2d[b], ctx->s_h2d));
+    // classify
+    NXS_CUDA(ctx, cudaStreamWaitEvent(s_comp, ctx->e_h2d[b], 0));
+    nxs_batch d_in{d_kind, d_reason, d_flags, d_stage, d_key, m};
+    nxs_out d_out{ctx->d_verdict[b], ctx->d_rows[b], ctx->d_njobs + b};
+    rc = launch_classify(ctx, &d_in, &d_out, (uint32_t)lo);
+    if (rc != NXS_OK) return rc;
+    NXS_CUDA(ctx, cudaEventRecord(ctx->e_kernel[b], s_comp));
+    // The previous slice's rows go out first (rows land in slice order, and the next upload into its
+    // buffer set waits only for them), then this slice's job count and verdicts.
+    if (pending[b ^ 1]) {
+      rc = finish_slice(b ^ 1);
+      if (rc != NXS_OK) return rc;
+    }
+    NXS_CUDA(ctx, cudaStreamWaitEvent(ctx->s_d2h, ctx->e_kernel[b], 0));
+    NXS_CUDA(ctx, cudaMemcpyAsync(ctx->h_njobs + b, ctx->d_njobs + b, 8, cudaMemcpyDeviceToHost, ctx->s_d2h));
+    NXS_CUDA(ctx, cudaEventRecord(ctx->e_count[b], ctx->s_d2h));
+    NXS_CUDA(ctx, cudaMemcpyAsync(out->verdict + lo, ctx->d_verdict[b], m * 4, cudaMemcpyDeviceToHost, ctx->s_d2h));
+    pend_lo[b] = lo;
+    pend_n[b] = m;
+    pending[b] = true;
+    lo = hi;
   }
-  NXS_CUDA(ctx, cudaMemcpyAsync(out->job_rows, ctx->d_rows, n_jobs * sizeof(nxs_job_row), cudaMemcpyDeviceToHost, st));
-  NXS_CUDA(ctx, cudaStreamSynchronize(st));
-  *out->n_jobs = n_jobs;
+  for (int b = 0; b < 2; ++b) {
+    // (at most one slice is left, but keep the order general: the older one first)
+    const int o = (pending[0] && pending[1] && pend_lo[1] < pend_lo[0]) ? (b ^ 1) : b;
+    if (pending[o]) {
+      rc = finish_slice(o);
+      if (rc != NXS_OK) return rc;
+    }
+  }
+  NXS_CUDA(ctx, cudaStreamSynchronize(ctx->s_d2h));
+  NXS_CUDA(ctx, cudaStreamSynchronize(s_comp));
+  *out->n_jobs = rows_done;
   return NXS_OK;
 }
 

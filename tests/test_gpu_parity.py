@@ -96,6 +96,19 @@ def test_tile_variants_and_context_reuse(tile, monkeypatch):
         assert c.launches == 5
 
 
+def test_host_path_slices_on_job_boundaries():
+    """The host-pointer entry point processes large batches in ~8M-record slices (upload, classify and
+    download overlapped); slices are cut on job boundaries and winner indices stay batch-relative."""
+    rng = np.random.default_rng(99)
+    n = 20_000_003
+    cols = util.random_cols(rng, n, 60, wide=False)
+    with nx.Classifier(device=0, max_records=n) as c:
+        for _ in range(2):  # the second call reuses the staging buffers and events
+            util.assert_same(*c.classify(cols), *cpu_oracle.classify(cols, threads=cpu_oracle.hardware_threads()),
+                             "sliced host path")
+        assert c.launches == 2 * 3
+
+
 def test_errors_are_reported_not_thrown(clf):
     with pytest.raises(nx.NxsError) as e:
         clf.classify(util.random_cols(np.random.default_rng(0), (1 << 23) + 1, 2))
