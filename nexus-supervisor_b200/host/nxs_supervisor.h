@@ -1,0 +1,157 @@
+// nxs_supervisor.h — host side of the classification path, in C++ (the reference is Go; no Go
+// toolchain exists on this box, so the mirror of its service interface is written above the C ABI
+// in C++).  Names, argument meaning and error behaviour follow services/supervisor.go of
+// SneaksAndData/nexus-supervisor:
+//
+//   reference                                         here
+//   ------------------------------------------------  -------------------------------------------
+//   ProcessingConfig                   :41-47          nxs_host::ProcessingConfig
+//   DecisionAction + constants         :49-56          nxs_host::ToFail... / ToRunning
+//   RunStatusAnalysisResult            :58-66          nxs_host::RunStatusAnalysisResult
+//   NewSupervisor(client, ns, store..) :69             Supervisor::Supervisor(...)
+//   (*Supervisor).Init                 :106            Supervisor::Init
+//   (*Supervisor).onEvent              :137            Supervisor::OnEvent   (flatten + enqueue)
+//   (*Supervisor).superviseAction      :261            Supervisor::Flush     (GPU verdicts -> I/O)
+//                                                      Supervisor::SuperviseAction (one result)
+//
+// What moves: the two string switches of onEvent and the decision part of superviseAction run
+// on the GPU for the whole batch (nxs_classify).  What stays on the host, unchanged in meaning:
+// the informer lookups (IsNexusRunEvent, GetCachedObject, labels), ReadCheckpoint before the batch,
+// Jobs().Delete and UpsertCheckpoint after it.  The supervisor as a whole stays bound by those
+// I/O calls (10 elements/s by default), whatever the classification costs.
+#pragma once
+#include <cstdint>
+#include <map>
+#include <optional>
+#include <string>
+#include <vector>
+
+#include "nxs_classify.h"
+
+namespace nxs_host {
+
+// ---- the slices of the Kubernetes / nexus-core types the path reads
+struct Event { // corev1.Event: the fields onEvent reads (:159,:171,:177-180)
+  std::string involved_kind, involved_name, involved_uid, reason, message;
+};
+struct CachedObject { // a Job or Pod from the informer cache: only its labels matter (:181,:231-232)
+  std::map<std::string, std::string> labels;
+};
+struct CheckpointedRequest { // nexus-core models.CheckpointedRequest: the columns the path touches
+  std::string algorithm, id, lifecycle_stage, algorithm_failure_cause, algorithm_failure_details;
+};
+
+// ---- the collaborators (interfaces so tests can fake them, like the reference's fake clientset)
+class ObjectCache { // resolvers.IsNexusRunEvent (:147) and resolvers.GetCachedObject[T] (:160,:211)
+ public:
+  virtual ~ObjectCache() = default;
+  virtual bool IsNexusRunEvent(const Event &event) = 0;
+  virtual std::optional<CachedObject> GetCachedObject(const std::string &kind, const std::string &name) = 0;
+};
+class CqlStore { // request.CqlStore: ReadCheckpoint (:264), UpsertCheckpoint (:301,:328,:353,:364)
+ public:
+  virtual ~CqlStore() = default;
+  virtual std::optional<CheckpointedRequest> ReadCheckpoint(const std::string &algorithm, const std::string &id) = 0;
+  virtual bool UpsertCheckpoint(const CheckpointedRequest &checkpoint) = 0;
+};
+class KubeClient { // kubeClient.BatchV1().Jobs(ns).Delete with background propagation (:268,:289,:314,:339)
+ public:
+  virtual ~KubeClient() = default;
+  virtual bool DeleteJob(const std::string &resource_namespace, const std::string &name) = 0;
+};
+
+struct ProcessingConfig { // :41-47 (delays in milliseconds)
+  int64_t FailureRateBaseDelayMs = 100;
+  int64_t FailureRateMaxDelayMs = 1000;
+  int RateLimitElementsPerSecond = 10;
+  int RateLimitElementsBurst = 100;
+  int Workers = 2;
+};
+
+using DecisionAction = std::string; // :49
+extern const DecisionAction ToFailStuckInPending, ToFailFatalError, ToFailDeadlineExceeded, ToRunning; // :52-55
+
+struct RunStatusAnalysisResult { // :58-66
+  DecisionAction Action;
+  std::string RunStatusMessage, RunStatusTrace, ObjectUID, ObjectKind, RequestId, Algorithm;
+};
+
+// nexus-core constants the reference only uses symbolically (values unpinned: not vendored).
+struct Vocabulary {
+  std::string JobTemplateNameKey = "science.sneaksanddata.com/algorithm-template-name";
+  std::string JobNameLabel = "batch.kubernetes.io/job-name"; // literal in the reference (:231)
+  std::string stage_names[8] = {"NEW",    "BUFFERED",          "RUNNING",           "COMPLETED",
+                                "FAILED", "SCHEDULING_FAILED", "DEADLINE_EXCEEDED", "CANCELLED"};
+  uint16_t finished_mask = NXS_FINISHED_MASK_DEFAULT; // stands in for (*CheckpointedRequest).IsFinished()
+};
+
+struct Error { // mirrors Go's `error`: empty message = nil
+  std::string message;
+  explicit operator bool() const { return !message.empty(); }
+};
+
+// What Flush did for one run (one job row): the observable effects of superviseAction.
+struct AppliedVerdict {
+  std::string algorithm, request_id;
+  uint32_t verdict = 0;
+  bool deleted_job = false, upserted = false, skipped_finished = false;
+  Error err; // "no checkpoint ..." mirrors the :265-273 path
+};
+
+class Supervisor {
+ public:
+  // NewSupervisor (:69): the Kubernetes client, the namespace and the store, plus the informer cache
+  // and the GPU the classification runs on.
+  Supervisor(KubeClient *client, std::string resource_namespace, CqlStore *cql_store, ObjectCache *cache,
+             int device = 0, Vocabulary vocabulary = Vocabulary());
+  ~Supervisor();
+  Supervisor(const Supervisor &) = delete;
+  Supervisor &operator=(const Supervisor &) = delete;
+
+  // Init (:106): creates the GPU context.  max_batch bounds the events between two Flush calls.
+  Error Init(const ProcessingConfig &config, uint64_t max_batch = 1u << 20);
+
+  // onEvent (:137): runs the guards' lookups, interns kind/reason, resolves RequestId/Algorithm from
+  // the labels and appends one record to the current batch.  Like the reference it never fails the
+  // caller: events it cannot use are dropped.
+  void OnEvent(const Event &event);
+  size_t PendingEvents() const { return events_.size(); }
+
+  // superviseAction (:261) for the whole batch: reads each run's checkpoint, classifies on the GPU,
+  // then deletes jobs / upserts checkpoints as the verdicts say.  Returns a non-empty error only for
+  // failures of the classification itself; per-run I/O outcomes are in `applied`.
+  Error Flush(std::vector<AppliedVerdict> *applied = nullptr);
+
+  // superviseAction (:261) for ONE analysis result, decided on the host from the same tables: the path
+  // a caller takes for a single retry.  Unknown actions return the reference's error text (:372).
+  Error SuperviseAction(const RunStatusAnalysisResult &result);
+
+  // The RunStatusAnalysisResult onEvent would have sent to the actor for a record of the last batch
+  // (empty Action when the event was dropped) — for tests that want to read like the reference's.
+  RunStatusAnalysisResult AnalysisResultOf(size_t event_index) const;
+
+ private:
+  struct Flat {
+    Event event;
+    std::string request_id, algorithm;
+    uint8_t kind = 0, flags = 0;
+    uint16_t reason = 0;
+    uint64_t job_key = 0;
+  };
+  Error Apply(const std::string &algorithm, const std::string &request_id, uint32_t verdict,
+              const std::string &trace, const std::optional<CheckpointedRequest> &checkpoint, AppliedVerdict *out);
+  KubeClient *client_;
+  std::string ns_;
+  CqlStore *store_;
+  ObjectCache *cache_;
+  int device_;
+  Vocabulary vocab_;
+  ProcessingConfig config_;
+  nxs_ctx *ctx_ = nullptr;
+  std::vector<Flat> events_, last_batch_;
+  std::vector<uint32_t> last_verdicts_;
+};
+
+uint64_t JobKey(const std::string &algorithm, const std::string &request_id); // hash of the checkpoint PK
+
+} // namespace nxs_host
