@@ -27,7 +27,7 @@ struct nxs_ctx {
   uint32_t gen = 0;
   uint64_t launches = 0;
   uint8_t lut[128];
-  uint8_t code[8];
+  uint16_t code[8];
   // staging for the host-pointer entry point (allocated on first use): two buffer sets, so the
   // upload of one slice overlaps the classification and the download of the previous one
   uint64_t staged_records = 0; // capacity of ONE set, in records

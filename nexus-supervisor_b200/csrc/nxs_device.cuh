@@ -72,6 +72,32 @@ __device__ __forceinline__ bool mbar_test_wait(uint64_t *bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Same on a precomputed shared-space address (saves the generic->shared conversion in hot loops).
+__device__ __forceinline__ bool mbar_test_wait_a(uint32_t bar_addr, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar_addr), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ bool mbar_try_wait_a(uint32_t bar_addr, uint32_t parity, uint32_t hint_ns) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar_addr), "r"(parity), "r"(hint_ns)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_arrive_a(uint32_t bar_addr) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_addr) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
@@ -112,8 +138,8 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
 #endif // __CUDACC__
 
 // ------------------------------------------------------- verdict arithmetic
-// LUT entry ("code") for one (kind, reason): action | cause_tpl << 3 | msg_tpl << 5;
-// 0 = `default`.
+// Code of a switch arm of onEvent = the low 12 bits of the verdict an applied record of that arm
+// gets: action | new_stage << 3 | cause_tpl << 7 | msg_tpl << 9; 0 = `default`.
 // applier switch (services/supervisor.go:283-370), indexed by action id
 __host__ __device__ __forceinline__ uint32_t new_stage_of(uint32_t action) {
   // 1 -> SCHEDULING_FAILED(5) :297, 2 -> FAILED(4) :324, 3 -> DEADLINE_EXCEEDED(6) :349, 4 -> RUNNING(2) :362
@@ -124,43 +150,41 @@ __host__ __device__ __forceinline__ uint32_t cause_tpl_of(uint32_t action) {
   return (0xE4u >> (action * 2)) & 3u;
 }
 __host__ __device__ __forceinline__ uint32_t make_code(uint32_t action, uint32_t msg_tpl) {
-  return action | cause_tpl_of(action) << 3 | msg_tpl << 5;
+  return action | new_stage_of(action) << 3 | cause_tpl_of(action) << 7 | msg_tpl << 9;
 }
 // Verdict of an APPLIED record with this action (msg_tpl added by the caller).
 __host__ __device__ __forceinline__ uint32_t applied_verdict(uint32_t action) {
   return NXS_V_PACK(action, new_stage_of(action), cause_tpl_of(action), 0, action != NXS_ACTION_RUNNING, 1,
                     0, 0);
 }
+constexpr uint32_t kCodeRunning = NXS_ACTION_RUNNING | NXS_STAGE_RUNNING << 3; // last applied record was a ToRunning
 
 // --------------------------------------------------------------- fold algebra
 // Summary of a run of consecutive records of ONE job, valid under the premise
 // "the row was not finished when the run began".  (If it was, nothing applies
-// and every handled record is a skip — summ_resolve handles that with s0.)
-// The low 16 bits sit where the packed verdict has the same fields, so closing a
-// job is mostly a mask.
+// and every handled record is a skip — summ_resolve handles that with F_FIN0.)
+// The low 16 bits ARE the packed verdict fields, so closing a job is a mask.
 struct Summ {
   uint32_t win_idx; // record index of the winner (if F_HAS_WIN)
   uint32_t f;
 };
 enum : uint32_t {
-  F_ALAST_MASK = 7u,      // bits 0-2: action of the last applied record (verdict.action)
-  F_WIN_SHIFT = 7,        // bits 7-8 cause_tpl, bits 9-11 msg_tpl of the winner (verdict.cause_tpl/msg_tpl)
-  F_WIN_MASK = 31u << 7,
+  F_LAST_MASK = 0x7Fu,    // bits 0-6: action and new stage of the last applied record (verdict.action/new_stage)
+  F_WIN_MASK = 31u << 7,  // bits 7-8 cause_tpl, 9-11 msg_tpl of the winner (verdict.cause_tpl/msg_tpl)
   F_HAS_WIN = 1u << 12,   // some applied record had a failure action (verdict.delete_job)
   F_HAS_APP = 1u << 13,   // some handled record with a checkpoint: applied under the premise (verdict.upsert)
   F_SKIP = 1u << 14,      // some handled record came after the stop (verdict.skip_finished)
   F_ERR = 1u << 15,       // some record had no checkpoint (verdict.err = 1)
-  F_STOPPED = 1u << 17,   // an applied record moved the row to a finished stage
-  F_S0_SHIFT = 18,        // bits 18-21: cur_stage of the job's first record (valid iff anchored)
-  F_S0_MASK = 15u << 18,
-  F_ANCHORED = 1u << 22,  // the run starts at the job's first record (look-back stops here)
-  F_BITS = 23
+  F_STOPPED = 1u << 16,   // an applied record moved the row to a finished stage
+  F_FIN0 = 1u << 17,      // the row was already finished at the job's first record (valid iff anchored)
+  F_ANCHORED = 1u << 18,  // the run starts at the job's first record (look-back stops here)
+  F_BITS = 19
 };
-constexpr uint32_t F_VERDICT_MASK = F_ALAST_MASK | F_WIN_MASK | F_HAS_WIN | F_HAS_APP | F_SKIP | F_ERR;
 
 __host__ __device__ __forceinline__ Summ summ_identity() { return Summ{0u, 0u}; }
-__host__ __device__ __forceinline__ Summ summ_anchor(uint32_t s0) {
-  return Summ{0u, ((s0 & 15u) << F_S0_SHIFT) | F_ANCHORED};
+// A run that begins at the job's first record; fin0 = IsFinished() of the row it found (:276).
+__host__ __device__ __forceinline__ Summ summ_anchor(bool fin0) {
+  return Summ{0u, F_ANCHORED | (fin0 ? F_FIN0 : 0u)};
 }
 __host__ __device__ __forceinline__ uint64_t summ_pack(Summ s) {
   return (uint64_t)s.f << 32 | s.win_idx;
@@ -172,16 +196,16 @@ __host__ __device__ __forceinline__ Summ summ_unpack(uint64_t v) {
 // L then R (L earlier in record order).  Associative.
 __host__ __device__ __forceinline__ Summ summ_combine(Summ L, Summ R) {
   uint32_t f = (L.f | R.f) & F_ERR;
-  f |= ((L.f & F_ANCHORED) ? L.f : R.f) & (F_S0_MASK | F_ANCHORED);
+  f |= ((L.f & F_ANCHORED) ? L.f : R.f) & (F_FIN0 | F_ANCHORED);
   uint32_t win;
   if (L.f & F_STOPPED) {
-    f |= L.f & (F_STOPPED | F_HAS_APP | F_ALAST_MASK | F_HAS_WIN | F_WIN_MASK | F_SKIP);
+    f |= L.f & (F_STOPPED | F_HAS_APP | F_LAST_MASK | F_HAS_WIN | F_WIN_MASK | F_SKIP);
     if (R.f & F_HAS_APP) f |= F_SKIP;
     win = L.win_idx;
   } else {
     f |= R.f & F_STOPPED;
     f |= (L.f | R.f) & (F_HAS_APP | F_SKIP);
-    f |= ((R.f & F_HAS_APP) ? R.f : L.f) & F_ALAST_MASK;
+    f |= ((R.f & F_HAS_APP) ? R.f : L.f) & F_LAST_MASK;
     const bool rw = (R.f & F_HAS_WIN) != 0;
     f |= (rw ? R.f : L.f) & (F_HAS_WIN | F_WIN_MASK);
     win = rw ? R.win_idx : L.win_idx;
@@ -229,15 +253,15 @@ __host__ __device__ __forceinline__ uint32_t summ_piece_flags(uint32_t he, uint3
   if (wm) f |= F_HAS_WIN;
   return f;
 }
-// Completes the flags with the winner's LUT code.
+// Completes the flags with the winner's code.
 __host__ __device__ __forceinline__ uint32_t summ_piece_finish(uint32_t f, uint32_t code_w, bool last_is_win) {
-  if (f & F_HAS_WIN) f |= (code_w >> 3) << F_WIN_SHIFT;
-  if (f & F_HAS_APP) f |= last_is_win ? (code_w & 7u) : (uint32_t)NXS_ACTION_RUNNING;
+  if (f & F_HAS_WIN) f |= code_w & F_WIN_MASK;
+  if (f & F_HAS_APP) f |= last_is_win ? (code_w & F_LAST_MASK) : kCodeRunning;
   return f;
 }
-// Convenience form with the codes in memory (host walk-through, long-job paths).
+// Convenience form with the codes in memory (host walk-through).
 __host__ __device__ __forceinline__ Summ summ_piece(uint32_t he, uint32_t term, uint32_t fail, uint32_t err,
-                                                    const uint8_t *code, uint32_t base, uint32_t global_base) {
+                                                    const uint16_t *code, uint32_t base, uint32_t global_base) {
   uint32_t wp;
   bool liw;
   const uint32_t f = summ_piece_flags(he, term, fail, err, wp, liw);
@@ -245,14 +269,10 @@ __host__ __device__ __forceinline__ Summ summ_piece(uint32_t he, uint32_t term, 
   return Summ{(f & F_HAS_WIN) ? global_base + base + wp : 0u, summ_piece_finish(f, cw, liw)};
 }
 
-// Close a job: apply the premise check with s0 and emit (verdict, winner_idx).
-__host__ __device__ __forceinline__ void summ_resolve(Summ s, uint32_t finished_mask, uint32_t &verdict,
-                                                      uint32_t &winner) {
-  const uint32_t s0 = (s.f >> F_S0_SHIFT) & 15u;
-  const bool fin0 = (finished_mask >> s0) & 1u;
-  uint32_t v;
-  if (fin0) v = ((s.f & F_HAS_APP) ? F_SKIP : 0u) | (s.f & F_ERR);
-  else v = (s.f & F_VERDICT_MASK) | new_stage_of(s.f & F_ALAST_MASK) << 3;
+// Close a job: apply the premise check and emit (verdict, winner_idx).
+__host__ __device__ __forceinline__ void summ_resolve(Summ s, uint32_t &verdict, uint32_t &winner) {
+  const bool fin0 = (s.f & F_FIN0) != 0;
+  const uint32_t v = fin0 ? (((s.f & F_HAS_APP) ? F_SKIP : 0u) | (s.f & F_ERR)) : (s.f & 0xFFFFu);
   verdict = v | (s.f & F_ERR) >> 3; // a missing checkpoint also deletes the job (:268)
   winner = (!fin0 && (s.f & F_HAS_WIN)) ? s.win_idx : NXS_NO_WINNER;
 }

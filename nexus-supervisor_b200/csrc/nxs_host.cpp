@@ -73,16 +73,18 @@ bool eq(const char *s, size_t len, const char *lit) { return strlen(lit) == len 
 } // namespace
 
 namespace nxs {
-void nxs_build_lut(uint8_t lut[128], uint8_t code[8]) {
+void nxs_build_lut(uint8_t lut[128], uint16_t code[8]) {
   memset(lut, 0, 128);
-  memset(code, 0, 8);
-  // cause template per action: :298, :325, :350, none for ToRunning
+  memset(code, 0, 8 * sizeof(uint16_t));
+  // applier switch per action: new stage (:297, :324, :349, :362) and cause template (:298, :325, :350)
+  static const uint8_t stage_of_action[5] = {0, NXS_STAGE_SCHEDULING_FAILED, NXS_STAGE_FAILED,
+                                             NXS_STAGE_DEADLINE_EXCEEDED, NXS_STAGE_RUNNING};
   static const uint8_t cause_of_action[5] = {0, 1, 2, 3, 0};
   uint8_t arm = 0;
   for (const SwitchArm &a : kSwitchArms) {
     ++arm;
     lut[a.kind * 32 + a.reason] = arm;
-    code[arm] = (uint8_t)(a.action | cause_of_action[a.action] << 3 | a.msg_tpl << 5);
+    code[arm] = (uint16_t)(a.action | stage_of_action[a.action] << 3 | cause_of_action[a.action] << 7 | a.msg_tpl << 9);
   }
 }
 } // namespace nxs

@@ -105,7 +105,7 @@ template <int STAGES> struct Ctl {
   uint32_t vt[32];   // [gate class 0..3][arm 0..7] -> verdict | fold bits
   uint8_t lut[128];  // (kind, reason) -> switch arm 1..7, 0 = `default`
   uint8_t lut2[128]; // (flags & 7) | stage << 3 -> 8 * gate class (0 dropped, 1 no checkpoint, 2 finished, 3 apply)
-  uint8_t code[8];   // arm -> action | cause_tpl << 3 | msg_tpl << 5
+  uint16_t code[8];  // arm -> action | new_stage << 3 | cause_tpl << 7 | msg_tpl << 9
 };
 
 // Tile descriptor: two self-validating 64-bit words, each published with one
@@ -152,7 +152,7 @@ struct ClassifyParams {
   uint32_t term_mask; // bit a: new_stage_of(a) is a finished stage
   uint32_t gen;
   uint8_t lut[128]; // (kind, reason) -> arm
-  uint8_t code[8];  // arm -> code
+  uint16_t code[8]; // arm -> code
 #ifdef NXS_TRACE
   unsigned long long *trace; // [0] = number of events, then (time, cta<<40 | event<<32 | tile) pairs
   uint32_t trace_cap;
@@ -316,18 +316,20 @@ __device__ __noinline__ void count_range(const ClassifyParams &p, StageBuf<TILE>
 struct CountStream {
   uint32_t s, par;
   bool end;
+  uint32_t full_addr, counted_addr; // shared-space addresses of ctl.full[0] / ctl.counted[0]
 };
-// Marks every tile that has landed since the last call (usually none or one).
+// Marks every tile that has landed since the last call (usually none or one).  The check itself is
+// four instructions; it runs between 64-record steps of the classification pass.
 template <int TILE, int STAGES>
-__device__ __forceinline__ void service_counts(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
-                                               CountStream &cs, uint32_t warp, uint32_t lane) {
-  while (!cs.end && __all_sync(0xffffffffu, mbar_test_wait(&ctl.full[cs.s], cs.par))) {
+__device__ __forceinline__ void service_counts(const ClassifyParams &p, StageBuf<TILE> *stages, CountStream &cs,
+                                               uint32_t warp, uint32_t lane) {
+  while (!cs.end && __all_sync(0xffffffffu, mbar_test_wait_a(cs.full_addr + 8u * cs.s, cs.par))) {
     StageBuf<TILE> &sb = stages[cs.s];
     const int32_t t = sb.tile;
     if (t < 0) cs.end = true;
     else count_range<TILE>(p, sb, (uint32_t)t, warp, lane);
     __syncwarp();
-    if (lane == 0) mbar_arrive(&ctl.counted[cs.s]);
+    if (lane == 0) mbar_arrive_a(cs.counted_addr + 8u * cs.s);
     if (++cs.s == STAGES) cs.s = 0, cs.par ^= 1u;
   }
 }
@@ -451,7 +453,7 @@ __device__ __forceinline__ void counter_loop(const ClassifyParams &p, StageBuf<T
 // ---------------------------------------------------------------------- workers
 template <int TILE, bool FULL, int STAGES>
 __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf<TILE> *stages, StageBuf<TILE> &sb,
-                                               Ctl<STAGES> &ctl, CountStream &cs, uint32_t tile, uint32_t warp,
+                                               const Ctl<STAGES> &ctl, CountStream &cs, uint32_t tile, uint32_t warp,
                                                uint32_t lane) {
   constexpr uint32_t RANGE = TILE / kWorkerWarps; // records per warp
   constexpr uint32_t CPW = RANGE / 32;            // 32-record chunks per warp
@@ -463,8 +465,8 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
     return;
   }
   const uint32_t gbase = p.record_base + start;
-  const uint32_t le = (2u << lane) - 1u, lt = le >> 1;
-  nxs_job_row *rows = p.rows + sb.tile_base + sb.range_off[warp];
+  const uint32_t le = (2u << lane) - 1u, lt = le >> 1, lanebit = 1u << lane;
+  const uint32_t row0 = sb.tile_base + sb.range_off[warp]; // index of the range's first job row
   // Does the first record of the range begin a job?  (warp-uniform)
   uint32_t prev_bit = r0 == 0 ? sb.first_is_head : sb.tailmask[r0 / 32 - 1] >> 31;
   const uint32_t first_is_head = prev_bit;
@@ -475,7 +477,7 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
 
 #pragma unroll kClassifyUnroll
   for (uint32_t j = 0; j < CPW; ++j) {
-    if (j) service_counts<TILE, STAGES>(p, stages, ctl, cs, warp, lane); // a tile that just landed goes first
+    if (j && (j & 1u) == 0) service_counts<TILE, STAGES>(p, stages, cs, warp, lane); // a tile that just landed goes first
     const uint32_t i = r0 + j * 32 + lane;
     const bool valid = FULL || i < cnt;
     const uint32_t T = sb.tailmask[r0 / 32 + j];
@@ -512,20 +514,20 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
     if (ER & seg) f |= F_ERR;
     if (tms) f |= F_STOPPED;
     if (hes & ~upto) f |= F_SKIP;
-    if (hes) f |= F_HAS_APP | NXS_ACTION_RUNNING; // a non-failure handled record is a ToRunning
+    if (hes) f |= F_HAS_APP | kCodeRunning; // a non-failure handled record is a ToRunning
     if (wm) {
-      f |= F_HAS_WIN | (code_w >> 3) << F_WIN_SHIFT;
-      if ((app >> wp) == 1u) f = (f & ~F_ALAST_MASK) | (code_w & 7u); // nothing applied after the winner
+      f |= F_HAS_WIN | (code_w & F_WIN_MASK);
+      if ((app >> wp) == 1u) f = (f & ~F_LAST_MASK) | (code_w & F_LAST_MASK); // nothing applied after the winner
     }
     Summ S{gbase + r0 + j * 32 + wp, f};
-    if (h_in) S.f |= st_head << F_S0_SHIFT | F_ANCHORED; // the job begins in this chunk
-    else S = summ_combine(ctx, S);                        // it continues the job left open before the chunk
+    if (h_in) S.f |= F_ANCHORED | (((p.finished_mask >> st_head) & 1u) ? F_FIN0 : 0u); // the job begins in this chunk
+    else S = summ_combine(ctx, S); // it continues the job left open before the chunk
 
-    if ((T >> lane) & 1u) { // this record ends a job: close it and store its row
+    if (T & lanebit) { // this record ends a job: close it and store its row
       if (S.f & F_ANCHORED) {
         uint32_t verdict, winner;
-        summ_resolve(S, p.finished_mask, verdict, winner);
-        __stcs(reinterpret_cast<uint4 *>(rows + wcount + __popc(T & lt)),
+        summ_resolve(S, verdict, winner);
+        __stcs(reinterpret_cast<uint4 *>(p.rows + (row0 + wcount + __popc(T & lt))),
                make_uint4((uint32_t)key, (uint32_t)(key >> 32), verdict, winner));
       } else { // only the first job of a range can have begun before it: left to the summary warp
         sb.range[warp].unres = summ_pack(S);
@@ -549,15 +551,14 @@ template <int TILE, int STAGES>
 __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
                                             uint32_t warp, uint32_t lane) {
   uint32_t s = 0, par = 0; // next tile to classify: stage, parity
-  CountStream cs{0u, 0u, false};
+  CountStream cs{0u, 0u, false, smem_u32(&ctl.full[0]), smem_u32(&ctl.counted[0])};
+  const uint32_t base_addr = smem_u32(&ctl.base_ready[0]), done_addr = smem_u32(&ctl.p1done[0]);
   Watchdog wd;
   while (true) {
-    service_counts<TILE, STAGES>(p, stages, ctl, cs, warp, lane);
-    // classify when the tile's first row index is known; otherwise sleep on whichever comes next
-    const bool ready = __all_sync(0xffffffffu, cs.end ? mbar_try_wait(&ctl.base_ready[s], par, 2000u)
-                                                      : mbar_test_wait(&ctl.base_ready[s], par));
-    if (!ready) {
-      if (!cs.end) (void)__all_sync(0xffffffffu, mbar_try_wait(&ctl.full[cs.s], cs.par, 500u));
+    service_counts<TILE, STAGES>(p, stages, cs, warp, lane);
+    // classify when the tile's first row index is known; otherwise sleep (briefly, so that a tile
+    // landing meanwhile is still marked promptly)
+    if (!__all_sync(0xffffffffu, mbar_try_wait_a(base_addr + 8u * s, par, cs.end ? 4000u : 1000u))) {
       wd.tick(p.counters + 2);
       continue;
     }
@@ -573,7 +574,7 @@ __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TI
       if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_END, (uint32_t)t);
     }
     __syncwarp();
-    if (lane == 0) mbar_arrive(&ctl.p1done[s]);
+    if (lane == 0) mbar_arrive_a(done_addr + 8u * s);
     if (t < 0) break;
     if (++s == STAGES) s = 0, par ^= 1u;
   }
@@ -680,7 +681,7 @@ __device__ __forceinline__ void summary_loop(const ClassifyParams &p, StageBuf<T
         const Summ S = summ_combine(acc, unres);
         if (S.f & F_ANCHORED) {
           uint32_t verdict, winner;
-          summ_resolve(S, p.finished_mask, verdict, winner);
+          summ_resolve(S, verdict, winner);
           __stcs(reinterpret_cast<uint4 *>(p.rows + rowpos),
                  make_uint4((uint32_t)ukey, (uint32_t)(ukey >> 32), verdict, winner));
         } else {
@@ -727,7 +728,7 @@ __device__ __forceinline__ void summary_loop(const ClassifyParams &p, StageBuf<T
           st_desc_word(&p.desc[tile].s, desc_s(summ_combine(st.carry, summ_unpack(q.local_summ)), DESC_INC, p.gen));
         if ((q.mask >> lane) & 1u) {
           uint32_t verdict, winner;
-          summ_resolve(summ_combine(st.carry, summ_unpack(q.unres[lane])), p.finished_mask, verdict, winner);
+          summ_resolve(summ_combine(st.carry, summ_unpack(q.unres[lane])), verdict, winner);
           const uint64_t key = q.key[lane];
           __stcs(reinterpret_cast<uint4 *>(p.rows + q.rowpos[lane]),
                  make_uint4((uint32_t)key, (uint32_t)(key >> 32), verdict, winner));
@@ -777,7 +778,7 @@ __global__ void __launch_bounds__(kThreads, TILE <= 2048 ? 2 : 1) classify_kerne
   if (tid < 8) ctl.code[tid] = p.code[tid];
   if (tid >= 128 && tid < 160) {
     const uint32_t e = tid - 128, g = e >> 3, arm = e & 7u;
-    const uint32_t code = p.code[arm], a = code & 7u, msg = code >> 5;
+    const uint32_t code = p.code[arm], a = code & 7u, msg = code >> 9;
     uint32_t v = 0;
     if (g != 0 && a >= 1 && a <= 4) {
       const uint32_t fold = VT_HE | (((p.term_mask >> a) & 1u) ? VT_TERM : 0u) | (a != NXS_ACTION_RUNNING ? VT_FAIL : 0u);

@@ -27,7 +27,8 @@ extern "C" int nxs_foldsim(const uint8_t *kind, const uint16_t *reason, const ui
                            const uint64_t *key, uint64_t n, uint16_t finished_mask, uint32_t tile_records,
                            uint64_t lookback_seed, uint32_t *verdict, nxs_job_row *rows, uint64_t *n_jobs) {
   if (tile_records == 0 || tile_records % 32) return -1;
-  uint8_t lut[128], code_of_arm[8];
+  uint8_t lut[128];
+  uint16_t code_of_arm[8];
   nxs_build_lut(lut, code_of_arm);
   uint32_t term_mask = 0;
   for (uint32_t a = 1; a <= 4; ++a)
@@ -35,7 +36,7 @@ extern "C" int nxs_foldsim(const uint8_t *kind, const uint16_t *reason, const ui
   const uint32_t TILE = tile_records, CHUNKS = TILE / 32;
   const uint64_t n_tiles = (n + TILE - 1) / TILE;
   std::vector<Desc> desc(n_tiles);
-  std::vector<uint8_t> code(TILE);
+  std::vector<uint16_t> code(TILE);
   std::vector<Masks> masks(CHUNKS);
   std::vector<uint32_t> chunk_off(CHUNKS);
   uint64_t rng = lookback_seed;
@@ -62,8 +63,8 @@ extern "C" int nxs_foldsim(const uint8_t *kind, const uint16_t *reason, const ui
         const bool finished = (finished_mask >> st) & 1u;
         const uint32_t base = exists ? (finished ? (a | 1u << 14) : (a ? applied_verdict(a) : 0u))
                                      : (a | 1u << 12 | NXS_ERR_NO_CHECKPOINT << 15);
-        verdict[g] = a ? (base | (cd >> 5) << 9) : 0u;
-        code[i] = (uint8_t)cd;
+        verdict[g] = a ? (base | (cd >> 9) << 9) : 0u;
+        code[i] = (uint16_t)cd;
         const bool he = a != 0 && exists;
         m.head |= (uint32_t)head << lane;
         m.tail |= (uint32_t)tail << lane;
@@ -95,7 +96,7 @@ extern "C" int nxs_foldsim(const uint8_t *kind, const uint16_t *reason, const ui
         S = summ_combine(S, summ_piece(w.he & mk, w.term & mk, w.fail & mk, w.err & mk, code.data(), c * 32,
                                        (uint32_t)start));
       }
-      T = last_head < 0 ? S : summ_combine(summ_anchor(stage[start + from]), S);
+      T = last_head < 0 ? S : summ_combine(summ_anchor((finished_mask >> (stage[start + from] & 15u)) & 1u), S);
     }
     desc[t].agg_count = total;
     desc[t].agg = T;
@@ -138,7 +139,7 @@ extern "C" int nxs_foldsim(const uint8_t *kind, const uint16_t *reason, const ui
         Summ S = carry;
         if (hm) {
           hbit = hi_bit(hm);
-          S = summ_anchor(stage[start + cc * 32 + hbit]);
+          S = summ_anchor((finished_mask >> (stage[start + cc * 32 + hbit] & 15u)) & 1u);
         }
         for (uint32_t k = cc; k <= c; ++k) {
           uint32_t mk = ~0u;
@@ -149,7 +150,7 @@ extern "C" int nxs_foldsim(const uint8_t *kind, const uint16_t *reason, const ui
                                          (uint32_t)start));
         }
         uint32_t v, win;
-        summ_resolve(S, finished_mask, v, win);
+        summ_resolve(S, v, win);
         rows[pos] = nxs_job_row{key[start + c * 32 + lane], v, win};
       }
     }
