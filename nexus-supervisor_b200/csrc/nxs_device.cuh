@@ -19,6 +19,13 @@ namespace nxs {
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
+// Shared-space address computed ONCE: the volatile asm keeps the compiler from re-deriving it (three
+// instructions: CTA id in cluster, shift, add) at every use inside hot or idle loops.
+__device__ __forceinline__ uint32_t smem_u32_pinned(const void *p) {
+  uint32_t a;
+  asm volatile("{\n\t.reg .u64 t;\n\tcvta.to.shared.u64 t, %1;\n\tcvt.u32.u64 %0, t;\n\t}" : "=r"(a) : "l"(p));
+  return a;
+}
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }

@@ -551,14 +551,15 @@ template <int TILE, int STAGES>
 __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
                                             uint32_t warp, uint32_t lane) {
   uint32_t s = 0, par = 0; // next tile to classify: stage, parity
-  CountStream cs{0u, 0u, false, smem_u32(&ctl.full[0]), smem_u32(&ctl.counted[0])};
-  const uint32_t base_addr = smem_u32(&ctl.base_ready[0]), done_addr = smem_u32(&ctl.p1done[0]);
+  CountStream cs{0u, 0u, false, smem_u32_pinned(&ctl.full[0]), smem_u32_pinned(&ctl.counted[0])};
+  const uint32_t base_addr = smem_u32_pinned(&ctl.base_ready[0]), done_addr = smem_u32_pinned(&ctl.p1done[0]);
   Watchdog wd;
   while (true) {
     service_counts<TILE, STAGES>(p, stages, cs, warp, lane);
-    // classify when the tile's first row index is known; otherwise sleep (briefly, so that a tile
-    // landing meanwhile is still marked promptly)
-    if (!__all_sync(0xffffffffu, mbar_try_wait_a(base_addr + 8u * s, par, cs.end ? 4000u : 1000u))) {
+    // classify when the tile's first row index is known; an idle warp sleeps off the issue slots and
+    // looks again (for a tile to mark or to classify) a few times per tile period
+    if (!__all_sync(0xffffffffu, mbar_test_wait_a(base_addr + 8u * s, par))) {
+      __nanosleep(600);
       wd.tick(p.counters + 2);
       continue;
     }
