@@ -12,9 +12,10 @@
 //                   (b)) each warp compares the adjacent job
 //                   keys of its range, leaves the "last record of a job" bit masks
 //                   and its job count in the stage;
-//   counter warp    sums the eight range counts, publishes the tile's JOB COUNT,
-//                   polls predecessor tiles (decoupled look-back on counts only)
-//                   for the index of the tile's first job row and releases (b)
+//   counter warps   (two, taking the CTA's tiles in turn) sum the range counts,
+//                   publish the tile's JOB COUNT, poll predecessor tiles (decoupled
+//                   look-back on counts only) for the index of the tile's first job
+//                   row and release (b)
 //   worker warps    (b) each warp owns a contiguous range of the tile and walks it 32
 //                   records at a time, lane per record: table lookups -> packed
 //                   verdict -> global; warp ballots -> bit masks in registers; the
@@ -40,9 +41,10 @@ namespace nxs {
 constexpr int kWorkerWarps = 16;
 constexpr int kWorkers = kWorkerWarps * 32;
 constexpr int kProducerWarp = kWorkerWarps;
-constexpr int kCounterWarp = kWorkerWarps + 1;
-constexpr int kSummaryWarp = kWorkerWarps + 2;
-constexpr int kThreads = kWorkers + 96;
+constexpr int kSummaryWarp = kWorkerWarps + 1;
+constexpr int kCounterWarp0 = kWorkerWarps + 2; // first of kCounterWarps counter warps
+constexpr int kCounterWarps = 2;                // tile k of a CTA is looked up by counter warp k % 2
+constexpr int kThreads = kWorkers + 64 + 32 * kCounterWarps;
 constexpr int kPendingSlots = 4;                // tiles whose carried-in summary is still being looked up
 constexpr uint64_t kWatchdogNs = 8000000000ull; // a stuck wait traps instead of hanging the GPU
 
@@ -75,7 +77,7 @@ template <int TILE> struct __align__(128) StageBuf {
   uint32_t tile_base;               // job rows before the tile
   uint32_t first_is_head;           // the tile's first record begins a job
   int32_t tile;                     // tile id, -1 = end of work
-  uint32_t pad;
+  uint32_t total;                   // jobs ending in the tile
 };
 
 // Verdict table entry = packed verdict of the record plus the fold bits above it.
@@ -101,6 +103,8 @@ template <int STAGES> struct Ctl {
   uint64_t base_ready[STAGES]; // first row index known    (counter warp -> workers)
   uint64_t p1done[STAGES];     // rows written             (workers -> summary warp)
   uint64_t freeb[STAGES];      // stage reusable           (summary warp -> producer)
+  uint32_t end_k;              // how many tiles this CTA claimed (set by the producer with the end marker)
+  uint32_t pad;
   PendingTile pending[kPendingSlots];
   uint32_t vt[32];   // [gate class 0..3][arm 0..7] -> verdict | fold bits
   uint8_t lut[128];  // (kind, reason) -> switch arm 1..7, 0 = `default`
@@ -235,6 +239,7 @@ __device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<
     const uint32_t id = next;
     if (id >= p.n_tiles) {
       sb.tile = -1;
+      *reinterpret_cast<volatile uint32_t *>(&ctl.end_k) = k;
       mbar_arrive_n(bar, 2);
       break;
     }
@@ -369,25 +374,28 @@ __device__ __forceinline__ bool count_lookback_poll(const ClassifyParams &p, Cou
   return false;
 }
 
+// Counter warp `which` handles the tiles k = which, which + kCounterWarps, ... of the CTA (k = order in
+// which the CTA claimed them), so that several look-backs are in flight per CTA: one look-back costs
+// a few L2 round trips, several times the time a tile may take at full speed.  Each warp is an event
+// loop: publishing the count of a freshly marked tile always comes before polling for an older one,
+// because every later tile of every CTA waits for that count.
 template <int TILE, int STAGES>
 __device__ __forceinline__ void counter_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
-                                             uint32_t lane) {
-  uint32_t kc = 0, sc = 0, parc = 0; // next tile to total: ordinal, stage, parity
-  uint32_t kb = 0, sbi = 0;          // next tile whose first row index is looked up
-  uint32_t totals[STAGES];           // job count of the tile in each stage
+                                             uint32_t which, uint32_t lane) {
+  uint32_t ka = which, kl = which; // next own tile to total / to look back for
   bool end = false, lb_active = false;
   CountLookback st{0, 0u};
   Watchdog wd;
   while (true) {
-    // Publishing the count of a marked tile comes first: it never waits on another CTA and every
-    // later tile needs it.
-    if (!end && __all_sync(0xffffffffu, mbar_test_wait(&ctl.counted[sc], parc))) {
-      StageBuf<TILE> &sb = stages[sc];
+    const uint32_t sa = ka % STAGES, para = (ka / STAGES) & 1u;
+    if (!end && __all_sync(0xffffffffu, mbar_test_wait(&ctl.counted[sa], para))) {
+      StageBuf<TILE> &sb = stages[sa];
       const int32_t t = sb.tile;
       if (t < 0) {
         end = true;
       } else {
-        if (lane == 0) NXS_TRACE_EVENT(p, EV_COUNT_START, (uint32_t)t);
+        const uint32_t tile = (uint32_t)t;
+        if (lane == 0) NXS_TRACE_EVENT(p, EV_COUNT_START, tile);
         const uint32_t mine = lane < (uint32_t)kWorkerWarps ? sb.range_cnt[lane] : 0u;
         uint32_t incl = mine;
 #pragma unroll
@@ -396,56 +404,53 @@ __device__ __forceinline__ void counter_loop(const ClassifyParams &p, StageBuf<T
           if ((int)lane >= d) incl += o;
         }
         if (lane < (uint32_t)kWorkerWarps) sb.range_off[lane] = incl - mine;
-        const uint32_t total = __shfl_sync(0xffffffffu, incl, kWorkerWarps - 1);
-#pragma unroll
-        for (int s = 0; s < STAGES; ++s)
-          if (s == (int)sc) totals[s] = total;
-        if (lane == 0) {
-          st_desc_word(&p.desc[t].c, desc_c(total, t == 0 ? DESC_INC : DESC_AGG, p.gen));
-          if (p.n_tiles == 1) *p.n_jobs = total;
+        if (lane == kWorkerWarps - 1) {
+          sb.total = incl;
+          st_desc_word(&p.desc[tile].c, desc_c(incl, tile == 0 ? DESC_INC : DESC_AGG, p.gen));
+          if (p.n_tiles == 1) *p.n_jobs = incl;
         }
-        if (lane == 0) NXS_TRACE_EVENT(p, EV_COUNT_END, (uint32_t)t);
-        ++kc;
-        if (++sc == STAGES) sc = 0, parc ^= 1u;
+        __syncwarp();
+        if (lane == 0) NXS_TRACE_EVENT(p, EV_COUNT_END, tile);
+        ka += kCounterWarps;
       }
       wd.reset();
       continue;
     }
-    if (kb < kc) { // look up the first row index of the oldest counted tile
-      StageBuf<TILE> &sb = stages[sbi];
+    if (kl < ka) { // look up the first row index of the oldest own tile (one round trip per poll)
+      const uint32_t sl = kl % STAGES;
+      StageBuf<TILE> &sb = stages[sl];
       const uint32_t tile = (uint32_t)sb.tile;
       if (!lb_active) {
-        st.pos = (int)tile - 1;
-        st.excl = 0;
+        st = CountLookback{(int)tile - 1, 0u};
         lb_active = true;
         if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_START, tile);
       }
       if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_POLL, tile);
       if (tile == 0 || count_lookback_poll(p, st, lane)) {
-        uint32_t total = 0;
-#pragma unroll
-        for (int s = 0; s < STAGES; ++s)
-          if (s == (int)sbi) total = totals[s];
         if (lane == 0) {
+          const uint32_t total = sb.total;
           if (tile != 0) st_desc_word(&p.desc[tile].c, desc_c(st.excl + total, DESC_INC, p.gen));
           if (tile == p.n_tiles - 1) *p.n_jobs = (uint64_t)st.excl + total;
           sb.tile_base = st.excl;
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(&ctl.base_ready[sbi]);
+        if (lane == 0) mbar_arrive(&ctl.base_ready[sl]);
         if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_END, tile);
         lb_active = false;
-        ++kb;
-        if (++sbi == STAGES) sbi = 0;
+        kl += kCounterWarps;
         wd.reset();
         continue;
       }
-    } else if (end) {
-      if (lane == 0) mbar_arrive(&ctl.base_ready[sc]); // wake the workers on the end marker
-      break;
-    } else {
-      (void)__all_sync(0xffffffffu, mbar_try_wait(&ctl.counted[sc], parc, 2000u));
+      wd.tick(p.counters + 2);
+      continue;
     }
+    if (end) { // this warp met the end marker: wake the workers
+      if (lane == 0) mbar_arrive(&ctl.base_ready[sa]);
+      break;
+    }
+    // the CTA's last tile may belong to another counter warp: stop once the claim count is known
+    if (*reinterpret_cast<volatile uint32_t *>(&ctl.end_k) < ka) break;
+    (void)__all_sync(0xffffffffu, mbar_try_wait(&ctl.counted[sa], para, 2000u));
     wd.tick(p.counters + 2);
   }
 }
@@ -751,7 +756,7 @@ __device__ __forceinline__ void summary_loop(const ClassifyParams &p, StageBuf<T
 }
 
 template <int TILE>
-__global__ void __launch_bounds__(kThreads, TILE <= 2048 ? 2 : 1) classify_kernel(const __grid_constant__ ClassifyParams p) {
+__global__ void __maxnreg__(48) classify_kernel(const __grid_constant__ ClassifyParams p) {
   constexpr int STAGES = StagesFor<TILE>::value;
   // (no manual re-alignment: keeping the pointer derived from the array keeps it in the shared
   // address space, so accesses compile to LDS/STS rather than generic loads)
@@ -777,6 +782,7 @@ __global__ void __launch_bounds__(kThreads, TILE <= 2048 ? 2 : 1) classify_kerne
         (uint8_t)(8u * ((fl & 3u) != 3u ? 0u : !(fl & NXS_FLAG_CHECKPOINT) ? 1u : ((p.finished_mask >> st) & 1u) ? 2u : 3u));
   }
   if (tid < 8) ctl.code[tid] = p.code[tid];
+  if (tid == 0) ctl.end_k = 0xFFFFFFFFu;
   if (tid >= 128 && tid < 160) {
     const uint32_t e = tid - 128, g = e >> 3, arm = e & 7u;
     const uint32_t code = p.code[arm], a = code & 7u, msg = code >> 9;
@@ -794,8 +800,8 @@ __global__ void __launch_bounds__(kThreads, TILE <= 2048 ? 2 : 1) classify_kerne
   if (warp < (uint32_t)kWorkerWarps) worker_loop<TILE, STAGES>(p, stages, ctl, warp, lane);
   else if (warp == (uint32_t)kProducerWarp) {
     if (lane == 0) producer_loop<TILE, STAGES>(p, stages, ctl);
-  } else if (warp == (uint32_t)kCounterWarp) counter_loop<TILE, STAGES>(p, stages, ctl, lane);
-  else summary_loop<TILE, STAGES>(p, stages, ctl, lane);
+  } else if (warp == (uint32_t)kSummaryWarp) summary_loop<TILE, STAGES>(p, stages, ctl, lane);
+  else counter_loop<TILE, STAGES>(p, stages, ctl, warp - kCounterWarp0, lane);
 }
 
 #endif // __CUDACC__
