@@ -217,6 +217,38 @@ Error Supervisor::SuperviseAction(const RunStatusAnalysisResult &r) {
   return Apply(r.Algorithm, r.RequestId, v, r.RunStatusTrace, row, &out);
 }
 
+std::string FailureCause(uint32_t cause_tpl, uint32_t msg_tpl) {
+  const char *fmt = nxs_cause_template(cause_tpl);
+  if (!fmt) return std::string();
+  const char *msg = nxs_msg_template(msg_tpl);
+  std::string cause(strlen(fmt) + strlen(msg) + 1, '\0');
+  cause.resize((size_t)snprintf(cause.data(), cause.size(), fmt, msg));
+  return cause;
+}
+
+std::vector<CheckpointUpdate> EncodeCheckpointRows(const nxs_job_row *rows, uint64_t n_rows, const Vocabulary &vocab) {
+  // the 4 x 7 possible cause strings are formatted once, not per row
+  std::string causes[4][7];
+  for (uint32_t c = 1; c < 4; ++c)
+    for (uint32_t m = 0; m < 7; ++m) causes[c][m] = FailureCause(c, m);
+  std::vector<CheckpointUpdate> out;
+  for (uint64_t r = 0; r < n_rows; ++r) {
+    const uint32_t v = rows[r].verdict;
+    if (!NXS_V_UPSERT(v)) continue;
+    CheckpointUpdate u;
+    u.job_row = (uint32_t)r;
+    u.lifecycle_stage = vocab.stage_names[NXS_V_NEW_STAGE(v) & 7];
+    u.delete_job = NXS_V_DELETE_JOB(v) != 0;
+    if (NXS_V_CAUSE_TPL(v)) {
+      u.sets_failure = true;
+      u.algorithm_failure_cause = causes[NXS_V_CAUSE_TPL(v)][NXS_V_MSG_TPL(v) % 7];
+      u.details_record = rows[r].winner_idx;
+    }
+    out.push_back(std::move(u));
+  }
+  return out;
+}
+
 RunStatusAnalysisResult Supervisor::AnalysisResultOf(size_t i) const {
   RunStatusAnalysisResult r;
   if (i >= last_batch_.size()) return r;

@@ -154,4 +154,23 @@ class Supervisor {
 
 uint64_t JobKey(const std::string &algorithm, const std::string &request_id); // hash of the checkpoint PK
 
+// ---- batched checkpoint-row encoder (the step right after the classification)
+// One UPDATE of nexus.checkpoints (test-resources/checkpoints.cql:1-23) per job row that calls for an
+// upsert: the three columns superviseAction mutates (:297-299, :324-326, :349-351, :362), keyed by the
+// row's position in the job-row array (the host maps it to (algorithm, id)).  Rows that only delete the
+// job, skip or fail produce no update.  `details_record` is the batch index of the event whose Message
+// becomes algorithm_failure_details, NXS_NO_WINNER when cause/details stay untouched (ToRunning).
+struct CheckpointUpdate {
+  uint32_t job_row;
+  std::string lifecycle_stage;
+  bool sets_failure = false; // false: only lifecycle_stage changes
+  std::string algorithm_failure_cause;
+  uint32_t details_record = NXS_NO_WINNER;
+  bool delete_job = false;
+};
+std::vector<CheckpointUpdate> EncodeCheckpointRows(const nxs_job_row *rows, uint64_t n_rows,
+                                                   const Vocabulary &vocabulary = Vocabulary());
+// The algorithm_failure_cause text for a (cause_tpl, msg_tpl) pair, e.g. T1 + M2 (:325 with :198).
+std::string FailureCause(uint32_t cause_tpl, uint32_t msg_tpl);
+
 } // namespace nxs_host

@@ -195,6 +195,28 @@ int main(int argc, char **argv) {
             row("alg", "twice2").algorithm_failure_cause == "Algorithm encountered a fatal error during execution: BackOff",
         "single-result path: %s", row("alg", "twice2").algorithm_failure_cause.c_str());
 
+  // batched checkpoint-row encoder: byte-exact cause strings, one update per upserting row
+  {
+    const nxs_job_row rows[5] = {
+        {1, NXS_V_PACK(NXS_ACTION_FATAL_ERROR, NXS_STAGE_FAILED, 2, 3, 1, 1, 0, 0), 7},          // Job/PodFailurePolicy
+        {2, NXS_V_PACK(NXS_ACTION_RUNNING, NXS_STAGE_RUNNING, 0, 0, 0, 1, 0, 0), NXS_NO_WINNER}, // Pod/Started
+        {3, NXS_V_PACK(0, 0, 0, 0, 0, 0, 1, 0), NXS_NO_WINNER},                                  // skipped: finished
+        {4, NXS_V_PACK(0, 0, 0, 0, 1, 0, 0, 1), NXS_NO_WINNER},                                  // no checkpoint
+        {5, NXS_V_PACK(NXS_ACTION_DEADLINE_EXCEEDED, NXS_STAGE_DEADLINE_EXCEEDED, 3, 2, 1, 1, 0, 0), 9}};
+    const auto ups = EncodeCheckpointRows(rows, 5);
+    CHECK(ups.size() == 3, "encoder: %zu updates", ups.size());
+    if (ups.size() == 3) {
+      CHECK(ups[0].lifecycle_stage == "FAILED" && ups[0].details_record == 7 && ups[0].delete_job &&
+                ups[0].algorithm_failure_cause == "Algorithm encountered a fatal error during execution: Algorithm "
+                                                  "encountered a fatal error during execution.",
+            "encoder row 0: %s", ups[0].algorithm_failure_cause.c_str());
+      CHECK(ups[1].lifecycle_stage == "RUNNING" && !ups[1].sets_failure && !ups[1].delete_job, "encoder row 1");
+      CHECK(ups[2].job_row == 4 && ups[2].algorithm_failure_cause ==
+                                       "Algorithm exceeded its max allowed run time limit or retry attempt count.",
+            "encoder row 2: %s", ups[2].algorithm_failure_cause.c_str());
+    }
+  }
+
   printf(failures ? "FAILED (%d checks)\n" : "ok: TestSupervisor scenarios and error paths pass\n", failures);
   return failures ? 1 : 0;
 }
