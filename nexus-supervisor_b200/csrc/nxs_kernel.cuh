@@ -107,7 +107,7 @@ template <int STAGES> struct Ctl {
   uint32_t pad;
   PendingTile pending[kPendingSlots];
   uint32_t vt[32];   // [gate class 0..3][arm 0..7] -> verdict | fold bits
-  uint8_t lut[128];  // (kind, reason) -> switch arm 1..7, 0 = `default`
+  uint8_t lut[136];  // [min(kind,3)][min(reason,32)] (row stride 33) -> switch arm 1..7, 0 = `default`
   uint8_t lut2[128]; // (flags & 7) | stage << 3 -> 8 * gate class (0 dropped, 1 no checkpoint, 2 finished, 3 apply)
   uint16_t code[8];  // arm -> action | new_stage << 3 | cause_tpl << 7 | msg_tpl << 9
 };
@@ -494,7 +494,7 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
       key = sb.keyx[2 + i];
       // onEvent: guards (:155,:161,:218) and the (kind, reason) switch arms, then superviseAction's
       // order: no checkpoint (:265) -> finished (:276) -> switch (:283).  All of it is table lookups.
-      const uint32_t arm = ctl.lut[min(kind, 3u) * 32u + (reason < 32u ? reason : 0u)];
+      const uint32_t arm = ctl.lut[min(kind, 3u) * 33u + min(reason, 32u)];
       code = ctl.code[arm];
       vt = ctl.vt[ctl.lut2[(fl & 7u) | st << 3] + arm];
       __stcs(p.verdict + start + i, vt & kVerdictMask);
@@ -775,8 +775,8 @@ __global__ void __maxnreg__(48) classify_kernel(const __grid_constant__ Classify
     }
     mbar_fence_init();
   }
+  if (tid < 136) ctl.lut[tid] = (tid < 132 && tid % 33u < 32u) ? p.lut[tid / 33u * 32u + tid % 33u] : 0;
   if (tid < 128) {
-    ctl.lut[tid] = p.lut[tid];
     const uint32_t fl = tid & 7u, st = tid >> 3;
     ctl.lut2[tid] =
         (uint8_t)(8u * ((fl & 3u) != 3u ? 0u : !(fl & NXS_FLAG_CHECKPOINT) ? 1u : ((p.finished_mask >> st) & 1u) ? 2u : 3u));
