@@ -109,6 +109,36 @@ def test_host_path_slices_on_job_boundaries():
         assert c.launches == 2 * 3
 
 
+def test_two_contexts_launching_concurrently():
+    """Two contexts on one GPU, each on its own stream, launched back to back without synchronising in
+    between: the kernels share the SMs, each context has its own tile counter and descriptors."""
+    import torch
+    n = 6_000_000
+    rng = np.random.default_rng(17)
+    runs = []
+    for i in range(2):
+        cols = util.random_cols(rng, n, 4 + 20 * i)
+        stream = torch.cuda.Stream()
+        clf = nx.Classifier(device=0, max_records=n, stream=stream.cuda_stream)
+        dev = {k: torch.from_numpy(v.view(np.uint8).copy()).cuda() for k, v in cols.items()}
+        out = (torch.empty(n, dtype=torch.int32, device="cuda"), torch.empty((n, 2), dtype=torch.int64, device="cuda"),
+               torch.zeros(1, dtype=torch.int64, device="cuda"))
+        runs.append((cols, stream, clf, dev, out))
+    torch.cuda.synchronize()
+    for _ in range(3):
+        for cols, stream, clf, dev, out in runs:
+            clf.classify_device(n, dev["kind"].data_ptr(), dev["reason_id"].data_ptr(), dev["flags"].data_ptr(),
+                                dev["cur_stage"].data_ptr(), dev["job_key"].data_ptr(), out[0].data_ptr(),
+                                out[1].data_ptr(), out[2].data_ptr())
+    torch.cuda.synchronize()
+    for cols, stream, clf, dev, out in runs:
+        want_v, want_r = cpu_oracle.classify(cols, threads=cpu_oracle.hardware_threads())
+        jobs = int(out[2].item())
+        got_r = out[1][:jobs].cpu().numpy().view(np.uint64).reshape(-1, 2).copy().view(cpu_oracle.JOB_ROW).reshape(-1)
+        util.assert_same(out[0].cpu().numpy().view(np.uint32), got_r, want_v, want_r, "concurrent contexts")
+        clf.close()
+
+
 def test_errors_are_reported_not_thrown(clf):
     with pytest.raises(nx.NxsError) as e:
         clf.classify(util.random_cols(np.random.default_rng(0), (1 << 23) + 1, 2))
