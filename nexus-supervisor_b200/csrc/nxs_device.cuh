@@ -56,6 +56,12 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity, ui
       : "memory");
   return ok != 0;
 }
+// 32-bit unsigned min as one instruction (the compiler otherwise builds 16-bit pair tricks around byte loads).
+__device__ __forceinline__ uint32_t umin32(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("min.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
 // Warp ballot of one bit of a word (one LOP3 + one VOTE).
 __device__ __forceinline__ uint32_t ballot_bit(uint32_t word, uint32_t bit) {
   uint32_t r;

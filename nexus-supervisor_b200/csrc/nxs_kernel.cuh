@@ -106,9 +106,10 @@ template <int STAGES> struct Ctl {
   uint32_t end_k;              // how many tiles this CTA claimed (set by the producer with the end marker)
   uint32_t pad;
   PendingTile pending[kPendingSlots];
-  uint32_t vt[32];   // [gate class 0..3][arm 0..7] -> verdict | fold bits
+  uint32_t vt[64];   // [finished(stage) 0..1][gate class 0..3][arm 0..7] -> verdict | fold bits (both halves equal)
   uint8_t lut[136];  // [min(kind,3)][min(reason,32)] (row stride 33) -> switch arm 1..7, 0 = `default`
   uint8_t lut2[128]; // (flags & 7) | stage << 3 -> 8 * gate class (0 dropped, 1 no checkpoint, 2 finished, 3 apply)
+                     //                             + 32 * IsFinished(stage)
   uint16_t code[8];  // arm -> action | new_stage << 3 | cause_tpl << 7 | msg_tpl << 9
 };
 
@@ -486,18 +487,20 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
     const uint32_t i = r0 + j * 32 + lane;
     const bool valid = FULL || i < cnt;
     const uint32_t T = sb.tailmask[r0 / 32 + j];
-    uint32_t st = 0, vt = 0, code = 0;
+    uint32_t fin_self = 0, vt = 0, code = 0;
     uint64_t key = 0;
     if (valid) {
       const uint32_t kind = sb.kind[i], reason = sb.reason[i], fl = sb.flags[i];
-      st = sb.stage[i] & 15u;
+      const uint32_t st = sb.stage[i] & 15u;
       key = sb.keyx[2 + i];
       // onEvent: guards (:155,:161,:218) and the (kind, reason) switch arms, then superviseAction's
       // order: no checkpoint (:265) -> finished (:276) -> switch (:283).  All of it is table lookups.
-      const uint32_t arm = ctl.lut[min(kind, 3u) * 33u + min(reason, 32u)];
+      const uint32_t arm = ctl.lut[umin32(kind, 3u) * 33u + umin32(reason, 32u)];
       code = ctl.code[arm];
-      vt = ctl.vt[ctl.lut2[(fl & 7u) | st << 3] + arm];
-      __stcs(p.verdict + start + i, vt & kVerdictMask);
+      const uint32_t l2 = ctl.lut2[(fl & 7u) | st << 3];
+      vt = ctl.vt[l2 + arm];
+      fin_self = (l2 << 12) & F_FIN0; // IsFinished() of the row this record saw (bit 5 of l2 -> bit 17)
+      __stcs(p.verdict + (start + i), vt & kVerdictMask);
     }
     const uint32_t H = T << 1 | prev_bit; // bit b: record b of the chunk begins a job
     prev_bit = T >> 31;
@@ -514,19 +517,18 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
     const uint32_t wm = app & FL;           // ... with a failure action
     const uint32_t wp = hi_bit(wm | 1u);    // the winner: the last of them
     const uint32_t code_w = __shfl_sync(0xffffffffu, code, wp);
-    const uint32_t st_head = __shfl_sync(0xffffffffu, st, hb);
-    uint32_t f = 0;
+    const uint32_t fin_head = __shfl_sync(0xffffffffu, fin_self, hb);
+    // summary flags: a non-failure handled record is a ToRunning; the winner brings cause / message, and
+    // action / stage too when nothing was applied after it
+    const uint32_t winbits = (code_w & (F_WIN_MASK | F_LAST_MASK)) | F_HAS_WIN | F_HAS_APP;
+    uint32_t f = hes ? (F_HAS_APP | kCodeRunning) : 0u;
+    if (wm) f = ((app >> wp) == 1u) ? winbits : (f | (winbits & ~F_LAST_MASK));
     if (ER & seg) f |= F_ERR;
     if (tms) f |= F_STOPPED;
     if (hes & ~upto) f |= F_SKIP;
-    if (hes) f |= F_HAS_APP | kCodeRunning; // a non-failure handled record is a ToRunning
-    if (wm) {
-      f |= F_HAS_WIN | (code_w & F_WIN_MASK);
-      if ((app >> wp) == 1u) f = (f & ~F_LAST_MASK) | (code_w & F_LAST_MASK); // nothing applied after the winner
-    }
     Summ S{gbase + r0 + j * 32 + wp, f};
-    if (h_in) S.f |= F_ANCHORED | (((p.finished_mask >> st_head) & 1u) ? F_FIN0 : 0u); // the job begins in this chunk
-    else S = summ_combine(ctx, S); // it continues the job left open before the chunk
+    if (h_in) S.f |= F_ANCHORED | fin_head; // the job begins in this chunk
+    else S = summ_combine(ctx, S);          // it continues the job left open before the chunk
 
     if (T & lanebit) { // this record ends a job: close it and store its row
       if (S.f & F_ANCHORED) {
@@ -778,13 +780,13 @@ __global__ void __maxnreg__(48) classify_kernel(const __grid_constant__ Classify
   if (tid < 136) ctl.lut[tid] = (tid < 132 && tid % 33u < 32u) ? p.lut[tid / 33u * 32u + tid % 33u] : 0;
   if (tid < 128) {
     const uint32_t fl = tid & 7u, st = tid >> 3;
-    ctl.lut2[tid] =
-        (uint8_t)(8u * ((fl & 3u) != 3u ? 0u : !(fl & NXS_FLAG_CHECKPOINT) ? 1u : ((p.finished_mask >> st) & 1u) ? 2u : 3u));
+    const uint32_t fin = (p.finished_mask >> st) & 1u;
+    ctl.lut2[tid] = (uint8_t)(8u * ((fl & 3u) != 3u ? 0u : !(fl & NXS_FLAG_CHECKPOINT) ? 1u : fin ? 2u : 3u) + 32u * fin);
   }
   if (tid < 8) ctl.code[tid] = p.code[tid];
   if (tid == 0) ctl.end_k = 0xFFFFFFFFu;
-  if (tid >= 128 && tid < 160) {
-    const uint32_t e = tid - 128, g = e >> 3, arm = e & 7u;
+  if (tid >= 128 && tid < 192) {
+    const uint32_t e = tid - 128, g = (e >> 3) & 3u, arm = e & 7u;
     const uint32_t code = p.code[arm], a = code & 7u, msg = code >> 9;
     uint32_t v = 0;
     if (g != 0 && a >= 1 && a <= 4) {
