@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libnxs_classify.so")
+LIB_PATH = os.environ.get("NXS_LIB") or os.path.join(_HERE, "lib", "libnxs_classify.so")  # NXS_LIB: tuning builds only
 
 NXS_OK = 0
 NXS_ERR_ARG, NXS_ERR_CAPACITY, NXS_ERR_CUDA, NXS_ERR_NO_DEVICE, NXS_ERR_NOMEM, NXS_ERR_UNKNOWN_ACTION = (

@@ -38,7 +38,10 @@
 
 namespace nxs {
 
-constexpr int kWorkerWarps = 16;
+#ifndef NXS_WORKERS
+#define NXS_WORKERS 8
+#endif
+constexpr int kWorkerWarps = NXS_WORKERS;
 constexpr int kWorkers = kWorkerWarps * 32;
 constexpr int kProducerWarp = kWorkerWarps;
 constexpr int kSummaryWarp = kWorkerWarps + 1;
@@ -563,12 +566,20 @@ __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TI
   Watchdog wd;
   while (true) {
     service_counts<TILE, STAGES>(p, stages, cs, warp, lane);
-    // classify when the tile's first row index is known; an idle warp sleeps off the issue slots and
-    // looks again (for a tile to mark or to classify) a few times per tile period
-    if (!__all_sync(0xffffffffu, mbar_test_wait_a(base_addr + 8u * s, par))) {
-      __nanosleep(600);
-      wd.tick(p.counters + 2);
-      continue;
+    // Classify when the tile's first row index is known.  Until then an idle warp sleeps off the issue
+    // slots in a loop kept as short as possible (two barrier tests, a nap): idle warps outnumber busy
+    // ones about half of the time and every instruction they issue is taken from a busy warp.
+    {
+      const uint32_t ready_addr = base_addr + 8u * s, landed_addr = cs.full_addr + 8u * cs.s;
+      bool ready;
+      while (true) {
+        ready = __all_sync(0xffffffffu, mbar_test_wait_a(ready_addr, par));
+        if (ready) break;
+        if (!cs.end && __all_sync(0xffffffffu, mbar_test_wait_a(landed_addr, cs.par))) break;
+        __nanosleep(500);
+        wd.tick(p.counters + 2);
+      }
+      if (!ready) continue; // a tile landed: mark it first
     }
     wd.reset();
     StageBuf<TILE> &sb = stages[s];
@@ -757,8 +768,11 @@ __device__ __forceinline__ void summary_loop(const ClassifyParams &p, StageBuf<T
   }
 }
 
+#ifndef NXS_MAXNREG
+#define NXS_MAXNREG 80
+#endif
 template <int TILE>
-__global__ void __maxnreg__(48) classify_kernel(const __grid_constant__ ClassifyParams p) {
+__global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__ ClassifyParams p) {
   constexpr int STAGES = StagesFor<TILE>::value;
   // (no manual re-alignment: keeping the pointer derived from the array keeps it in the shared
   // address space, so accesses compile to LDS/STS rather than generic loads)
