@@ -46,7 +46,10 @@ constexpr int kWorkers = kWorkerWarps * 32;
 constexpr int kProducerWarp = kWorkerWarps;
 constexpr int kSummaryWarp = kWorkerWarps + 1;
 constexpr int kCounterWarp0 = kWorkerWarps + 2; // first of kCounterWarps counter warps
-constexpr int kCounterWarps = 2;                // tile k of a CTA is looked up by counter warp k % 2
+#ifndef NXS_COUNTER_WARPS
+#define NXS_COUNTER_WARPS 2
+#endif
+constexpr int kCounterWarps = NXS_COUNTER_WARPS;                // tile k of a CTA is looked up by counter warp k % 2
 constexpr int kThreads = kWorkers + 64 + 32 * kCounterWarps;
 constexpr int kPendingSlots = 4;                // tiles whose carried-in summary is still being looked up
 constexpr uint64_t kWatchdogNs = 8000000000ull; // a stuck wait traps instead of hanging the GPU
@@ -173,6 +176,12 @@ template <int TILE> constexpr size_t classify_smem_bytes() {
 
 #if defined(__CUDACC__)
 
+#ifndef NXS_IDLE_NS
+#define NXS_IDLE_NS 500
+#endif
+#ifndef NXS_POLL_MASK
+#define NXS_POLL_MASK 0xFFFFFFFFu /* never inside a range: measured slower (it splits the instruction stream) */
+#endif
 #ifndef NXS_CLASSIFY_UNROLL
 #define NXS_CLASSIFY_UNROLL 2
 #endif
@@ -348,7 +357,10 @@ struct CountLookback {
   int pos;       // nearest predecessor tile of the next window
   uint32_t excl; // job rows counted so far
 };
-constexpr int kCountWindows = 8;
+#ifndef NXS_COUNT_WINDOWS
+#define NXS_COUNT_WINDOWS 2
+#endif
+constexpr int kCountWindows = NXS_COUNT_WINDOWS;
 // One non-blocking step of the count look-back: kCountWindows x 32 predecessor count
 // words in one round trip (independent loads), consumed 32 at a time, nearest first.
 // A window is consumed only when every word it needs has been published.
@@ -464,6 +476,7 @@ template <int TILE, bool FULL, int STAGES>
 __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf<TILE> *stages, StageBuf<TILE> &sb,
                                                const Ctl<STAGES> &ctl, CountStream &cs, uint32_t tile, uint32_t warp,
                                                uint32_t lane) {
+  static_assert(TILE % (kWorkerWarps * 32) == 0, "a tile is split evenly into 32-record steps per worker warp");
   constexpr uint32_t RANGE = TILE / kWorkerWarps; // records per warp
   constexpr uint32_t CPW = RANGE / 32;            // 32-record chunks per warp
   const uint32_t start = tile * TILE;
@@ -486,7 +499,7 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
 
 #pragma unroll kClassifyUnroll
   for (uint32_t j = 0; j < CPW; ++j) {
-    if (j && (j & 1u) == 0) service_counts<TILE, STAGES>(p, stages, cs, warp, lane); // a tile that just landed goes first
+    if (j && (j & NXS_POLL_MASK) == 0) service_counts<TILE, STAGES>(p, stages, cs, warp, lane); // a tile that just landed goes first
     const uint32_t i = r0 + j * 32 + lane;
     const bool valid = FULL || i < cnt;
     const uint32_t T = sb.tailmask[r0 / 32 + j];
@@ -576,7 +589,7 @@ __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TI
         ready = __all_sync(0xffffffffu, mbar_test_wait_a(ready_addr, par));
         if (ready) break;
         if (!cs.end && __all_sync(0xffffffffu, mbar_test_wait_a(landed_addr, cs.par))) break;
-        __nanosleep(500);
+        __nanosleep(NXS_IDLE_NS);
         wd.tick(p.counters + 2);
       }
       if (!ready) continue; // a tile landed: mark it first
@@ -604,7 +617,10 @@ struct SummLookback {
   int pos;
   Summ carry;
 };
-constexpr int kSummWindows = 2;
+#ifndef NXS_SUMM_WINDOWS
+#define NXS_SUMM_WINDOWS 2
+#endif
+constexpr int kSummWindows = NXS_SUMM_WINDOWS;
 // One non-blocking step of the summary look-back: walks predecessor summary words,
 // nearest first, until one is anchored (holds the first record of the job).
 __device__ __forceinline__ bool summ_lookback_poll(const ClassifyParams &p, SummLookback &st, uint32_t lane) {
