@@ -19,7 +19,7 @@ struct nxs_ctx {
   uint64_t max_records = 0;
   uint32_t finished_mask = 0;
   uint32_t term_mask = 0;
-  int tile = 2048;        // records per tile (kernel variant)
+  int tile = NXS_TILE_DEFAULT; // records per tile (kernel variant)
   int ctas_per_sm = 1;    // resident CTAs of the chosen variant
   uint32_t max_tiles = 0;
   TileDesc *desc = nullptr;
@@ -134,10 +134,10 @@ int nxs_create(int device, uint64_t max_records, uint16_t finished_mask, nxs_ctx
   if (prop.major < 10) return bail(NXS_ERR_NO_DEVICE); // sm_100a code only
   ctx->num_sms = prop.multiProcessorCount;
   const char *tile_env = getenv("NXS_TILE");
-  ctx->tile = tile_env ? atoi(tile_env) : 2048;
-  if (ctx->tile == 1024) rc = configure_variant<1024>(ctx);
-  else if (ctx->tile == 2048) rc = configure_variant<2048>(ctx);
-  else if (ctx->tile == 4096) rc = configure_variant<4096>(ctx);
+  ctx->tile = tile_env ? atoi(tile_env) : NXS_TILE_DEFAULT;
+  if (ctx->tile == NXS_TILE_S) rc = configure_variant<NXS_TILE_S>(ctx);
+  else if (ctx->tile == NXS_TILE_M) rc = configure_variant<NXS_TILE_M>(ctx);
+  else if (ctx->tile == NXS_TILE_L) rc = configure_variant<NXS_TILE_L>(ctx);
   else rc = NXS_ERR_ARG;
   if (rc != NXS_OK) return bail(rc);
   if (getenv("NXS_VERBOSE"))
@@ -261,9 +261,9 @@ static int launch_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out
   const uint32_t max_grid = (uint32_t)(ctx->num_sms * ctx->ctas_per_sm);
   const uint32_t grid = p.n_tiles < max_grid ? p.n_tiles : max_grid;
   int rc;
-  if (ctx->tile == 1024) rc = launch_variant<1024>(ctx, p, grid);
-  else if (ctx->tile == 2048) rc = launch_variant<2048>(ctx, p, grid);
-  else rc = launch_variant<4096>(ctx, p, grid);
+  if (ctx->tile == NXS_TILE_S) rc = launch_variant<NXS_TILE_S>(ctx, p, grid);
+  else if (ctx->tile == NXS_TILE_M) rc = launch_variant<NXS_TILE_M>(ctx, p, grid);
+  else rc = launch_variant<NXS_TILE_L>(ctx, p, grid);
   if (rc == NXS_OK) ctx->launches += 1;
   return rc;
 }
@@ -446,8 +446,8 @@ void nxs_free_host(void *p) {
 // `g_noalloc_scratch` as written in host code is only a host-side handle for the
 // symbol, never a device address: the address each device gave the array is
 // looked up once per device with cudaGetSymbolAddress and handed to the kernel.
-constexpr int kNoallocTile = 2048;
-constexpr uint32_t kNoallocMaxTiles = NXS_NOALLOC_MAX_RECORDS / kNoallocTile;
+constexpr int kNoallocTile = NXS_TILE_DEFAULT;
+constexpr uint32_t kNoallocMaxTiles = (NXS_NOALLOC_MAX_RECORDS + kNoallocTile - 1) / kNoallocTile;
 constexpr size_t kNoallocCounterBytes = 256;
 constexpr size_t kNoallocScratchBytes = kNoallocCounterBytes + sizeof(TileDesc) * kNoallocMaxTiles;
 static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoallocScratchBytes];

@@ -8,15 +8,12 @@
 //   producer warp   claims tile ids from a global counter and streams the five
 //                   input columns of a tile into a stage with 1-D bulk async
 //                   copies (TMA engine, SASS UBLKCP)
-//   worker warps    (a) as soon as a tile has landed (checked between two tiles of
-//                   (b)) each warp compares the adjacent job
-//                   keys of its range, leaves the "last record of a job" bit masks
-//                   and its job count in the stage;
-//   counter warps   (two, taking the CTA's tiles in turn) sum the range counts,
-//                   publish the tile's JOB COUNT, poll predecessor tiles (decoupled
-//                   look-back on counts only) for the index of the tile's first job
-//                   row and release (b)
-//   worker warps    (b) each warp owns a contiguous range of the tile and walks it 32
+//   counter warps   (two, taking the CTA's tiles in turn) as soon as a tile has landed:
+//                   compare the adjacent job keys, leave the "last record of a job" bit
+//                   masks and the jobs-per-range offsets in the stage, publish the tile's
+//                   JOB COUNT, poll predecessor tiles (decoupled look-back on counts only)
+//                   for the index of the tile's first job row and release the workers
+//   worker warps    each warp owns a contiguous range of the tile and walks it 32
 //                   records at a time, lane per record: table lookups -> packed
 //                   verdict -> global; warp ballots -> bit masks in registers; the
 //                   lane holding the last record of a job folds the job's masks
@@ -32,6 +29,7 @@
 // Splitting the look-back in two keeps the stage's residency short: the count is
 // known as soon as the keys have landed, so row positions are ready before the
 // expensive pass starts and no stage waits for another CTA's classification.
+// The worker warps run nothing but the classification pass and wait on one barrier.
 // Scratch: TileDesc[n_tiles] (16 B each) + 3 counters.
 #pragma once
 #include "nxs_device.cuh"
@@ -49,13 +47,40 @@ constexpr int kCounterWarp0 = kWorkerWarps + 2; // first of kCounterWarps counte
 #ifndef NXS_COUNTER_WARPS
 #define NXS_COUNTER_WARPS 2
 #endif
-constexpr int kCounterWarps = NXS_COUNTER_WARPS;                // tile k of a CTA is looked up by counter warp k % 2
+constexpr int kCounterWarps = NXS_COUNTER_WARPS; // tile k of a CTA is counted and looked up by counter warp k % kCounterWarps
 constexpr int kThreads = kWorkers + 64 + 32 * kCounterWarps;
 constexpr int kPendingSlots = 4;                // tiles whose carried-in summary is still being looked up
 constexpr uint64_t kWatchdogNs = 8000000000ull; // a stuck wait traps instead of hanging the GPU
 
+// The three tile sizes built into the library (NXS_TILE selects one at run time); each must
+// be a multiple of 32 * NXS_WORKERS.
+#ifndef NXS_TILE_S
+#define NXS_TILE_S 1024
+#endif
+#ifndef NXS_TILE_M
+#define NXS_TILE_M 2048
+#endif
+#ifndef NXS_TILE_L
+#define NXS_TILE_L 4096
+#endif
+#ifndef NXS_TILE_DEFAULT
+#define NXS_TILE_DEFAULT NXS_TILE_M
+#endif
+// Ring depth: as many stages as fit in half an SM's shared memory (two CTAs per SM), 2..NXS_MAX_STAGES.
+#ifndef NXS_MAX_STAGES
+#define NXS_MAX_STAGES 4
+#endif
+#ifndef NXS_SMEM_BUDGET_KB
+#define NXS_SMEM_BUDGET_KB 110
+#endif
+constexpr int kStageBudgetBytes = NXS_SMEM_BUDGET_KB * 1024;
 template <int TILE> struct StagesFor {
-  static constexpr int value = TILE <= 2048 ? 4 : 2;
+  static constexpr int per_stage = TILE * 13 + TILE / 8 + 256 + 48 * NXS_WORKERS; // ~ sizeof(StageBuf<TILE>)
+  static constexpr int fit = kStageBudgetBytes / per_stage;
+  static constexpr int capped = fit < 2 ? 2 : fit > NXS_MAX_STAGES ? NXS_MAX_STAGES : fit;
+  // a multiple of the number of counter warps, so that a stage always belongs to the same counter warp
+  static constexpr int value = capped / NXS_COUNTER_WARPS * NXS_COUNTER_WARPS;
+  static_assert(value >= NXS_COUNTER_WARPS, "a tile this large leaves too few stages");
 };
 
 // What a worker warp leaves behind for its range of the tile.
@@ -78,7 +103,6 @@ template <int TILE> struct __align__(128) StageBuf {
   uint8_t stage[TILE];
   uint32_t tailmask[TILE / 32]; // bit b: record 32*chunk + b is the last of its job
   RangeInfo range[kWorkerWarps];
-  uint32_t range_cnt[kWorkerWarps]; // jobs ending in each range
   uint32_t range_off[kWorkerWarps]; // jobs ending before each range, tile-local
   uint32_t tile_base;               // job rows before the tile
   uint32_t first_is_head;           // the tile's first record begins a job
@@ -105,7 +129,6 @@ struct PendingTile {
 
 template <int STAGES> struct Ctl {
   uint64_t full[STAGES];       // tile landed              (producer -> workers)
-  uint64_t counted[STAGES];    // job boundaries marked    (workers -> counter warp)
   uint64_t base_ready[STAGES]; // first row index known    (counter warp -> workers)
   uint64_t p1done[STAGES];     // rows written             (workers -> summary warp)
   uint64_t freeb[STAGES];      // stage reusable           (summary warp -> producer)
@@ -179,9 +202,6 @@ template <int TILE> constexpr size_t classify_smem_bytes() {
 #ifndef NXS_IDLE_NS
 #define NXS_IDLE_NS 500
 #endif
-#ifndef NXS_POLL_MASK
-#define NXS_POLL_MASK 0xFFFFFFFFu /* never inside a range: measured slower (it splits the instruction stream) */
-#endif
 #ifndef NXS_CLASSIFY_UNROLL
 #define NXS_CLASSIFY_UNROLL 2
 #endif
@@ -215,6 +235,27 @@ __device__ __forceinline__ void trace_event(const ClassifyParams &p, uint32_t ev
 #define NXS_TRACE_EVENT(p, ev, tile) ((void)0)
 #endif
 
+// Naps of the service warps between two polls (0 = none).  The hardware scheduler prefers the
+// warps with the higher ids — the service warps — so every poll they issue is taken from a worker.
+#ifndef NXS_PRODUCER_NS
+#define NXS_PRODUCER_NS 0
+#endif
+#ifndef NXS_COUNTER_NS
+#define NXS_COUNTER_NS 0
+#endif
+#ifndef NXS_COUNT_LB_NS
+#define NXS_COUNT_LB_NS 0
+#endif
+#ifndef NXS_SUMMARY_NS
+#define NXS_SUMMARY_NS 0
+#endif
+#ifndef NXS_SUMM_LB_NS
+#define NXS_SUMM_LB_NS 0
+#endif
+template <unsigned NS> __device__ __forceinline__ void aux_nap() {
+  if (NS > 0) __nanosleep(NS);
+}
+
 struct Watchdog {
   uint64_t t0;
   uint32_t spins;
@@ -244,7 +285,10 @@ __device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<
   for (uint32_t k = 0;; ++k) {
     const uint32_t s = k % STAGES, use = k / STAGES;
     if (use > 0) {
-      while (!mbar_try_wait(&ctl.freeb[s], (use - 1) & 1u, 20000u)) wd.tick(p.counters + 2);
+      while (!mbar_try_wait(&ctl.freeb[s], (use - 1) & 1u, 20000u)) {
+        aux_nap<NXS_PRODUCER_NS>();
+        wd.tick(p.counters + 2);
+      }
       wd.reset();
     }
     StageBuf<TILE> &sb = stages[s];
@@ -283,34 +327,39 @@ __device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<
   }
 }
 
-// ------------------------------------------------------ job boundaries (workers)
-// One worker warp marks the job boundaries of its range of a landed tile: the "last
-// record of its job" masks and the number of jobs ending in the range.  Warp 0 also
-// notes whether the tile's first record begins a job.  A ragged (last) tile is read
-// from global memory here and copied into the stage for the classification pass.
+// -------------------------------------------------------- job boundaries (counter warp)
+// Marks the job boundaries of a landed tile: the "last record of its job" bit masks, the
+// number of jobs ending before each worker range, whether the tile's first record begins a
+// job; returns the tile's job count (warp-uniform).  A ragged (last) tile is read from
+// global memory here and copied into the stage for the classification pass.
 template <int TILE>
-__device__ __noinline__ void count_range(const ClassifyParams &p, StageBuf<TILE> &sb, uint32_t tile, uint32_t warp,
-                                         uint32_t lane) {
+__device__ __forceinline__ uint32_t count_tile(const ClassifyParams &p, StageBuf<TILE> &sb, uint32_t tile,
+                                                uint32_t lane) {
   constexpr uint32_t RANGE = TILE / kWorkerWarps, CPW = RANGE / 32;
   const uint32_t start = tile * TILE;
   const uint32_t cnt = min((uint32_t)TILE, p.n - start);
-  const uint32_t r0 = warp * RANGE;
-  uint32_t jobs = 0;
+  uint32_t total = 0;
   if (cnt == (uint32_t)TILE) {
     const bool last_tile = start + cnt == p.n;
+#pragma unroll 1
+    for (uint32_t r = 0; r < (uint32_t)kWorkerWarps; ++r) {
+      uint32_t jobs = 0;
 #pragma unroll
-    for (uint32_t j = 0; j < CPW; ++j) {
-      const uint32_t i = r0 + j * 32 + lane;
-      bool tail = sb.keyx[2 + i] != sb.keyx[3 + i];
-      if (last_tile && i == TILE - 1) tail = true;
-      const uint32_t T = __ballot_sync(0xffffffffu, tail);
-      if (lane == 0) sb.tailmask[r0 / 32 + j] = T;
-      jobs += __popc(T);
+      for (uint32_t j = 0; j < CPW; ++j) {
+        const uint32_t i = r * RANGE + j * 32 + lane;
+        bool tail = sb.keyx[2 + i] != sb.keyx[3 + i];
+        if (last_tile && i == TILE - 1) tail = true;
+        const uint32_t T = __ballot_sync(0xffffffffu, tail);
+        if (lane == 0) sb.tailmask[r * CPW + j] = T;
+        jobs += __popc(T);
+      }
+      if (lane == 0) sb.range_off[r] = total;
+      total += jobs;
     }
-    if (warp == 0 && lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(sb.keyx[2] != sb.keyx[1]);
-  } else { // ragged last tile (once per launch)
-    for (uint32_t j = 0; j < CPW; ++j) {
-      const uint32_t i = r0 + j * 32 + lane;
+    if (lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(sb.keyx[2] != sb.keyx[1]);
+  } else { // ragged last tile (once per launch): read from global memory, copied into the stage
+    for (uint32_t c = 0; c < (uint32_t)TILE / 32; ++c) {
+      const uint32_t i = c * 32 + lane;
       bool tail = false;
       if (i < cnt) {
         const uint64_t key = p.key[start + i];
@@ -322,34 +371,15 @@ __device__ __noinline__ void count_range(const ClassifyParams &p, StageBuf<TILE>
         sb.stage[i] = p.stage[start + i];
       }
       const uint32_t T = __ballot_sync(0xffffffffu, tail);
-      if (lane == 0) sb.tailmask[r0 / 32 + j] = T;
-      jobs += __popc(T);
+      if (lane == 0) {
+        if (c % CPW == 0) sb.range_off[c / CPW] = total;
+        sb.tailmask[c] = T;
+      }
+      total += __popc(T);
     }
-    if (warp == 0 && lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(p.key[start] != p.key[start - 1]);
+    if (lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(p.key[start] != p.key[start - 1]);
   }
-  if (lane == 0) sb.range_cnt[warp] = jobs;
-}
-
-// What a worker warp remembers about the tiles it still has to mark.
-struct CountStream {
-  uint32_t s, par;
-  bool end;
-  uint32_t full_addr, counted_addr; // shared-space addresses of ctl.full[0] / ctl.counted[0]
-};
-// Marks every tile that has landed since the last call (usually none or one).  The check itself is
-// four instructions; it runs between 64-record steps of the classification pass.
-template <int TILE, int STAGES>
-__device__ __forceinline__ void service_counts(const ClassifyParams &p, StageBuf<TILE> *stages, CountStream &cs,
-                                               uint32_t warp, uint32_t lane) {
-  while (!cs.end && __all_sync(0xffffffffu, mbar_test_wait_a(cs.full_addr + 8u * cs.s, cs.par))) {
-    StageBuf<TILE> &sb = stages[cs.s];
-    const int32_t t = sb.tile;
-    if (t < 0) cs.end = true;
-    else count_range<TILE>(p, sb, (uint32_t)t, warp, lane);
-    __syncwarp();
-    if (lane == 0) mbar_arrive_a(cs.counted_addr + 8u * cs.s);
-    if (++cs.s == STAGES) cs.s = 0, cs.par ^= 1u;
-  }
+  return total;
 }
 
 // ----------------------------------------------------------------- counter warp
@@ -393,18 +423,21 @@ __device__ __forceinline__ bool count_lookback_poll(const ClassifyParams &p, Cou
 // Counter warp `which` handles the tiles k = which, which + kCounterWarps, ... of the CTA (k = order in
 // which the CTA claimed them), so that several look-backs are in flight per CTA: one look-back costs
 // a few L2 round trips, several times the time a tile may take at full speed.  Each warp is an event
-// loop: publishing the count of a freshly marked tile always comes before polling for an older one,
-// because every later tile of every CTA waits for that count.
+// loop: counting a freshly landed tile and publishing its count always comes before polling for an
+// older one, because every later tile of every CTA waits for that count.  (The ring depth is a
+// multiple of kCounterWarps: a stage's `full` barrier is only ever watched by one counter warp, in
+// phase order — a parity wait cannot tell a phase from the one two before it.)
 template <int TILE, int STAGES>
 __device__ __forceinline__ void counter_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
                                              uint32_t which, uint32_t lane) {
-  uint32_t ka = which, kl = which; // next own tile to total / to look back for
+  uint32_t ka = which, kl = which; // next own tile to count / to look back for
   bool end = false, lb_active = false;
   CountLookback st{0, 0u};
   Watchdog wd;
   while (true) {
     const uint32_t sa = ka % STAGES, para = (ka / STAGES) & 1u;
-    if (!end && __all_sync(0xffffffffu, mbar_test_wait(&ctl.counted[sa], para))) {
+    uint64_t *const arrival = &ctl.full[sa]; // the counter warp marks the job boundaries itself
+    if (!end && __all_sync(0xffffffffu, mbar_test_wait(arrival, para))) {
       StageBuf<TILE> &sb = stages[sa];
       const int32_t t = sb.tile;
       if (t < 0) {
@@ -412,15 +445,8 @@ __device__ __forceinline__ void counter_loop(const ClassifyParams &p, StageBuf<T
       } else {
         const uint32_t tile = (uint32_t)t;
         if (lane == 0) NXS_TRACE_EVENT(p, EV_COUNT_START, tile);
-        const uint32_t mine = lane < (uint32_t)kWorkerWarps ? sb.range_cnt[lane] : 0u;
-        uint32_t incl = mine;
-#pragma unroll
-        for (int d = 1; d < kWorkerWarps; d <<= 1) {
-          const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
-          if ((int)lane >= d) incl += o;
-        }
-        if (lane < (uint32_t)kWorkerWarps) sb.range_off[lane] = incl - mine;
-        if (lane == kWorkerWarps - 1) {
+        const uint32_t incl = count_tile<TILE>(p, sb, tile, lane);
+        if (lane == 0) {
           sb.total = incl;
           st_desc_word(&p.desc[tile].c, desc_c(incl, tile == 0 ? DESC_INC : DESC_AGG, p.gen));
           if (p.n_tiles == 1) *p.n_jobs = incl;
@@ -457,6 +483,7 @@ __device__ __forceinline__ void counter_loop(const ClassifyParams &p, StageBuf<T
         wd.reset();
         continue;
       }
+      aux_nap<NXS_COUNT_LB_NS>();
       wd.tick(p.counters + 2);
       continue;
     }
@@ -466,16 +493,15 @@ __device__ __forceinline__ void counter_loop(const ClassifyParams &p, StageBuf<T
     }
     // the CTA's last tile may belong to another counter warp: stop once the claim count is known
     if (*reinterpret_cast<volatile uint32_t *>(&ctl.end_k) < ka) break;
-    (void)__all_sync(0xffffffffu, mbar_try_wait(&ctl.counted[sa], para, 2000u));
+    if (!__all_sync(0xffffffffu, mbar_try_wait(arrival, para, 2000u))) aux_nap<NXS_COUNTER_NS>();
     wd.tick(p.counters + 2);
   }
 }
 
 // ---------------------------------------------------------------------- workers
 template <int TILE, bool FULL, int STAGES>
-__device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf<TILE> *stages, StageBuf<TILE> &sb,
-                                               const Ctl<STAGES> &ctl, CountStream &cs, uint32_t tile, uint32_t warp,
-                                               uint32_t lane) {
+__device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf<TILE> &sb, const Ctl<STAGES> &ctl,
+                                               uint32_t tile, uint32_t warp, uint32_t lane) {
   static_assert(TILE % (kWorkerWarps * 32) == 0, "a tile is split evenly into 32-record steps per worker warp");
   constexpr uint32_t RANGE = TILE / kWorkerWarps; // records per warp
   constexpr uint32_t CPW = RANGE / 32;            // 32-record chunks per warp
@@ -499,7 +525,6 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
 
 #pragma unroll kClassifyUnroll
   for (uint32_t j = 0; j < CPW; ++j) {
-    if (j && (j & NXS_POLL_MASK) == 0) service_counts<TILE, STAGES>(p, stages, cs, warp, lane); // a tile that just landed goes first
     const uint32_t i = r0 + j * 32 + lane;
     const bool valid = FULL || i < cnt;
     const uint32_t T = sb.tailmask[r0 / 32 + j];
@@ -574,25 +599,15 @@ template <int TILE, int STAGES>
 __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
                                             uint32_t warp, uint32_t lane) {
   uint32_t s = 0, par = 0; // next tile to classify: stage, parity
-  CountStream cs{0u, 0u, false, smem_u32_pinned(&ctl.full[0]), smem_u32_pinned(&ctl.counted[0])};
   const uint32_t base_addr = smem_u32_pinned(&ctl.base_ready[0]), done_addr = smem_u32_pinned(&ctl.p1done[0]);
   Watchdog wd;
   while (true) {
-    service_counts<TILE, STAGES>(p, stages, cs, warp, lane);
     // Classify when the tile's first row index is known.  Until then an idle warp sleeps off the issue
-    // slots in a loop kept as short as possible (two barrier tests, a nap): idle warps outnumber busy
-    // ones about half of the time and every instruction they issue is taken from a busy warp.
-    {
-      const uint32_t ready_addr = base_addr + 8u * s, landed_addr = cs.full_addr + 8u * cs.s;
-      bool ready;
-      while (true) {
-        ready = __all_sync(0xffffffffu, mbar_test_wait_a(ready_addr, par));
-        if (ready) break;
-        if (!cs.end && __all_sync(0xffffffffu, mbar_test_wait_a(landed_addr, cs.par))) break;
-        __nanosleep(NXS_IDLE_NS);
-        wd.tick(p.counters + 2);
-      }
-      if (!ready) continue; // a tile landed: mark it first
+    // slots in a loop kept as short as possible (a barrier test, a nap): every instruction an idle warp
+    // issues is taken from a busy one.
+    while (!__all_sync(0xffffffffu, mbar_test_wait_a(base_addr + 8u * s, par))) {
+      __nanosleep(NXS_IDLE_NS);
+      wd.tick(p.counters + 2);
     }
     wd.reset();
     StageBuf<TILE> &sb = stages[s];
@@ -600,9 +615,9 @@ __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TI
     if (t >= 0) {
       if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_START, (uint32_t)t);
       if (p.n - (uint32_t)t * TILE >= (uint32_t)TILE)
-        classify_range<TILE, true, STAGES>(p, stages, sb, ctl, cs, (uint32_t)t, warp, lane);
+        classify_range<TILE, true, STAGES>(p, sb, ctl, (uint32_t)t, warp, lane);
       else
-        classify_range<TILE, false, STAGES>(p, stages, sb, ctl, cs, (uint32_t)t, warp, lane);
+        classify_range<TILE, false, STAGES>(p, sb, ctl, (uint32_t)t, warp, lane);
       if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_END, (uint32_t)t);
     }
     __syncwarp();
@@ -775,10 +790,11 @@ __device__ __forceinline__ void summary_loop(const ClassifyParams &p, StageBuf<T
         wd.reset();
         continue;
       }
+      aux_nap<NXS_SUMM_LB_NS>();
     } else if (end) {
       break;
     } else {
-      (void)__all_sync(0xffffffffu, mbar_try_wait(&ctl.p1done[s], par, 2000u));
+      if (!__all_sync(0xffffffffu, mbar_try_wait(&ctl.p1done[s], par, 2000u))) aux_nap<NXS_SUMMARY_NS>();
     }
     wd.tick(p.counters + 2);
   }
@@ -800,7 +816,6 @@ __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&ctl.full[s], 2);
-      mbar_init(&ctl.counted[s], kWorkerWarps);
       mbar_init(&ctl.base_ready[s], 1);
       mbar_init(&ctl.p1done[s], kWorkerWarps);
       mbar_init(&ctl.freeb[s], 1);

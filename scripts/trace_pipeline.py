@@ -13,7 +13,7 @@ sys.path.insert(0, ROOT)
 import nexus_supervisor_b200 as nx  # noqa: E402
 from nexus_supervisor_b200 import _abi  # noqa: E402
 
-_abi.LIB_PATH = os.path.join(ROOT, "nexus-supervisor_b200", "lib", "libnxs_classify_trace.so")
+_abi.LIB_PATH = os.environ.get("NXS_TRACE_LIB") or os.path.join(ROOT, "nexus-supervisor_b200", "lib", "libnxs_classify_trace.so")
 import torch  # noqa: E402
 
 EV = {1: "claim", 2: "issued", 3: "count_start", 4: "count_end", 5: "lb_start", 6: "lb_end", 7: "p1_start",
