@@ -142,6 +142,18 @@ __device__ __forceinline__ void st_relaxed(uint64_t *p, uint64_t v) {
 __device__ __forceinline__ void st_release(uint64_t *p, uint64_t v) {
   asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+// Loads from tables in shared memory that do not change after start-up, by 32-bit shared address
+// (the address arithmetic is then exactly what is written: one instruction per table index).
+__device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
+  uint32_t v;
+  asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
 __device__ __forceinline__ uint64_t global_timer_ns() {
   uint64_t t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));

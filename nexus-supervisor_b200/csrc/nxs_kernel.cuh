@@ -135,11 +135,13 @@ template <int STAGES> struct Ctl {
   uint32_t end_k;              // how many tiles this CTA claimed (set by the producer with the end marker)
   uint32_t pad;
   PendingTile pending[kPendingSlots];
-  uint32_t vt[64];   // [finished(stage) 0..1][gate class 0..3][arm 0..7] -> verdict | fold bits (both halves equal)
-  uint8_t lut[136];  // [min(kind,3)][min(reason,32)] (row stride 33) -> switch arm 1..7, 0 = `default`
-  uint8_t lut2[128]; // (flags & 7) | stage << 3 -> 8 * gate class (0 dropped, 1 no checkpoint, 2 finished, 3 apply)
-                     //                             + 32 * IsFinished(stage)
-  uint16_t code[8];  // arm -> action | new_stage << 3 | cause_tpl << 7 | msg_tpl << 9
+  // Tables of the classification pass.  Entries are pre-scaled to byte offsets so that an address is
+  // one instruction: vt entry of a record = vt + lut[..] + lut2[..].
+  alignas(16) uint32_t vt[64]; // [finished(stage) 0..1][gate class 0..3][arm 0..7] -> verdict | fold bits (both halves equal)
+  uint32_t code[8];            // arm -> action | new_stage << 3 | cause_tpl << 7 | msg_tpl << 9
+  uint8_t lut[136];            // [min(kind,3)][min(reason,32)] (row stride 33) -> 4 * switch arm (1..7, 0 = `default`)
+  alignas(8) uint8_t lut2[2048]; // stage * 8 + (flags & 7) -> 32 * gate class (0 dropped, 1 no checkpoint, 2 finished,
+                                 //                            3 apply) + 128 * IsFinished(stage & 15)
 };
 
 // Tile descriptor: two self-validating 64-bit words, each published with one
@@ -222,7 +224,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
 #ifdef NXS_TRACE
 // Debug build only: CTAs 0, 97 and 211 log pipeline events with the global timer.
 enum : uint32_t { EV_CLAIM = 1, EV_ISSUED, EV_COUNT_START, EV_COUNT_END, EV_LB_START, EV_LB_END, EV_P1_START,
-                  EV_P1_END, EV_SUM_START, EV_SUM_END, EV_LB_POLL, EV_SLB_END };
+                  EV_P1_END, EV_SUM_START, EV_SUM_END, EV_LB_POLL, EV_SLB_END, EV_STEP };
 __device__ __forceinline__ void trace_event(const ClassifyParams &p, uint32_t ev, uint32_t tile) {
   if (!p.trace || !(blockIdx.x == 0 || blockIdx.x == 97 || blockIdx.x == 211)) return;
   const unsigned long long i = atomicAdd(p.trace, 1ull);
@@ -512,7 +514,6 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
     if (lane == 0) sb.range[warp] = RangeInfo{summ_pack(summ_identity()), 0ull, 0ull, 0u, 0u};
     return;
   }
-  const uint32_t gbase = p.record_base + start;
   const uint32_t le = (2u << lane) - 1u, lt = le >> 1, lanebit = 1u << lane;
   const uint32_t row0 = sb.tile_base + sb.range_off[warp]; // index of the range's first job row
   // Does the first record of the range begin a job?  (warp-uniform)
@@ -523,25 +524,34 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
   if (lane == 0) sb.range[warp].has_unres = 0;
   __syncwarp();
 
+  // running pointers (bumped once per step: no index arithmetic inside the loop)
+  const uint32_t i0 = r0 + lane;
+  const uint8_t *pk = sb.kind + i0, *pf = sb.flags + i0, *ps = sb.stage + i0;
+  const uint16_t *pr = sb.reason + i0;
+  const uint64_t *pkey = sb.keyx + 2 + i0;
+  const uint32_t *pt = sb.tailmask + r0 / 32;
+  uint32_t *pv = p.verdict + (start + i0);
+  uint32_t gidx = p.record_base + start + r0; // batch index of the step's first record
+  const uint32_t lut_a = smem_u32_pinned(ctl.lut), lut2_a = smem_u32_pinned(ctl.lut2);
+  const uint32_t vt_a = smem_u32_pinned(ctl.vt), code_a = smem_u32_pinned(ctl.code);
+
 #pragma unroll kClassifyUnroll
-  for (uint32_t j = 0; j < CPW; ++j) {
-    const uint32_t i = r0 + j * 32 + lane;
-    const bool valid = FULL || i < cnt;
-    const uint32_t T = sb.tailmask[r0 / 32 + j];
+  for (uint32_t j = 0; j < CPW; ++j, pk += 32, pf += 32, ps += 32, pr += 32, pkey += 32, pt += 1, pv += 32, gidx += 32) {
+    const bool valid = FULL || i0 + j * 32 < cnt;
+    const uint32_t T = *pt;
     uint32_t fin_self = 0, vt = 0, code = 0;
     uint64_t key = 0;
     if (valid) {
-      const uint32_t kind = sb.kind[i], reason = sb.reason[i], fl = sb.flags[i];
-      const uint32_t st = sb.stage[i] & 15u;
-      key = sb.keyx[2 + i];
+      const uint32_t kind = *pk, reason = *pr, fl = *pf, st = *ps;
+      key = *pkey;
       // onEvent: guards (:155,:161,:218) and the (kind, reason) switch arms, then superviseAction's
       // order: no checkpoint (:265) -> finished (:276) -> switch (:283).  All of it is table lookups.
-      const uint32_t arm = ctl.lut[umin32(kind, 3u) * 33u + umin32(reason, 32u)];
-      code = ctl.code[arm];
-      const uint32_t l2 = ctl.lut2[(fl & 7u) | st << 3];
-      vt = ctl.vt[l2 + arm];
-      fin_self = (l2 << 12) & F_FIN0; // IsFinished() of the row this record saw (bit 5 of l2 -> bit 17)
-      __stcs(p.verdict + (start + i), vt & kVerdictMask);
+      const uint32_t arm4 = lds_u8(lut_a + umin32(kind, 3u) * 33u + umin32(reason, 32u));
+      code = lds_u32(code_a + arm4);
+      const uint32_t l2 = lds_u8(st * 8u + ((fl & 7u) | lut2_a)); // lut2 is 8-byte aligned: | is +
+      vt = lds_u32(vt_a + arm4 + l2);
+      fin_self = (l2 << 10) & F_FIN0; // IsFinished() of the row this record saw (bit 7 of l2 -> bit 17)
+      __stcs(pv, vt & kVerdictMask);
     }
     const uint32_t H = T << 1 | prev_bit; // bit b: record b of the chunk begins a job
     prev_bit = T >> 31;
@@ -567,7 +577,7 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
     if (ER & seg) f |= F_ERR;
     if (tms) f |= F_STOPPED;
     if (hes & ~upto) f |= F_SKIP;
-    Summ S{gbase + r0 + j * 32 + wp, f};
+    Summ S{gidx + wp, f};
     if (h_in) S.f |= F_ANCHORED | fin_head; // the job begins in this chunk
     else S = summ_combine(ctx, S);          // it continues the job left open before the chunk
 
@@ -584,9 +594,12 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
       }
     }
     wcount += __popc(T);
-    if (FULL || r0 + j * 32 + 31 < cnt) closed = T >> 31;
+    if (FULL || r0 + j * 32 + 31 < cnt) closed = T >> 31; // (FULL: compile time)
     else closed = 1; // the ragged (hence last) tile ends inside this chunk: its last record closes a job
     ctx = shfl_summ(S, 31);
+#ifdef NXS_TRACE_STEPS
+    if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_STEP, tile | j << 24);
+#endif
   }
   __syncwarp();
   if (lane == 0) {
@@ -822,11 +835,11 @@ __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__
     }
     mbar_fence_init();
   }
-  if (tid < 136) ctl.lut[tid] = (tid < 132 && tid % 33u < 32u) ? p.lut[tid / 33u * 32u + tid % 33u] : 0;
-  if (tid < 128) {
-    const uint32_t fl = tid & 7u, st = tid >> 3;
+  if (tid < 136) ctl.lut[tid] = (tid < 132 && tid % 33u < 32u) ? (uint8_t)(4u * p.lut[tid / 33u * 32u + tid % 33u]) : 0;
+  for (uint32_t e = tid; e < 2048u; e += kThreads) {
+    const uint32_t fl = e & 7u, st = (e >> 3) & 15u;
     const uint32_t fin = (p.finished_mask >> st) & 1u;
-    ctl.lut2[tid] = (uint8_t)(8u * ((fl & 3u) != 3u ? 0u : !(fl & NXS_FLAG_CHECKPOINT) ? 1u : fin ? 2u : 3u) + 32u * fin);
+    ctl.lut2[e] = (uint8_t)(32u * ((fl & 3u) != 3u ? 0u : !(fl & NXS_FLAG_CHECKPOINT) ? 1u : fin ? 2u : 3u) + 128u * fin);
   }
   if (tid < 8) ctl.code[tid] = p.code[tid];
   if (tid == 0) ctl.end_k = 0xFFFFFFFFu;

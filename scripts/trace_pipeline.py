@@ -46,10 +46,13 @@ def main():
     t0 = int(ev[:, 0].min())
     per = {}
     polls = {}
+    steps = {}
     for t, w in ev:
         cta, e, tile = int(w) >> 40, (int(w) >> 32) & 255, int(w) & 0xFFFFFFFF
         if e == 11:
             polls[(cta, tile)] = polls.get((cta, tile), 0) + 1
+        elif e == 13:  # NXS_TRACE_STEPS build: end of 32-record step j of warp 0
+            steps.setdefault((cta, tile & 0xFFFFFF), {})[tile >> 24] = int(t) - t0
         else:
             per.setdefault((cta, tile), {})[EV[e]] = int(t) - t0
     print(f"{cnt} events, span {(int(ev[:, 0].max()) - t0) / 1e3:.1f} us")
@@ -76,6 +79,13 @@ def main():
                 print(f"{tile:6d} {d['claim'] / 1e3:8.1f} | " + " ".join(f"{vals[k]:6d}" for k in cols))
         print(" median: " + "  ".join(f"{k}={int(np.median(v))}" for k, v in agg.items() if v))
         print(" mean:   " + "  ".join(f"{k}={int(np.mean(v))}" for k, v in agg.items() if v))
+        st = [(per[k]["p1_start"], per[k].get("p1_end"), steps[k]) for k in steps if k[0] == cta and "p1_start" in per.get(k, {})]
+        if st:
+            nj = max(len(x[2]) for x in st)
+            first = np.median([x[2][0] - x[0] for x in st if 0 in x[2]])
+            later = [np.median([x[2][j] - x[2][j - 1] for x in st if j in x[2] and j - 1 in x[2]]) for j in range(1, nj)]
+            tail = np.median([x[1] - x[2][nj - 1] for x in st if x[1] and nj - 1 in x[2]])
+            print(f" steps of warp 0 (ns): start->step0 {int(first)}  step j-1->j {[int(v) for v in later]}  last step->end {int(tail)}")
         if len(tiles) > 1:
             claims = np.array([per[(cta, t)]["claim"] for t in tiles if "claim" in per[(cta, t)]])
             print(f" tile period (claim to claim): median {int(np.median(np.diff(np.sort(claims))))} ns")
