@@ -45,7 +45,7 @@ constexpr int kProducerWarp = kWorkerWarps;
 constexpr int kSummaryWarp = kWorkerWarps + 1;
 constexpr int kCounterWarp0 = kWorkerWarps + 2; // first of kCounterWarps counter warps
 #ifndef NXS_COUNTER_WARPS
-#define NXS_COUNTER_WARPS 2
+#define NXS_COUNTER_WARPS 4
 #endif
 constexpr int kCounterWarps = NXS_COUNTER_WARPS; // tile k of a CTA is counted and looked up by counter warp k % kCounterWarps
 constexpr int kThreads = kWorkers + 64 + 32 * kCounterWarps;
@@ -77,10 +77,7 @@ constexpr int kStageBudgetBytes = NXS_SMEM_BUDGET_KB * 1024;
 template <int TILE> struct StagesFor {
   static constexpr int per_stage = TILE * 13 + TILE / 8 + 256 + 48 * NXS_WORKERS; // ~ sizeof(StageBuf<TILE>)
   static constexpr int fit = kStageBudgetBytes / per_stage;
-  static constexpr int capped = fit < 2 ? 2 : fit > NXS_MAX_STAGES ? NXS_MAX_STAGES : fit;
-  // a multiple of the number of counter warps, so that a stage always belongs to the same counter warp
-  static constexpr int value = capped / NXS_COUNTER_WARPS * NXS_COUNTER_WARPS;
-  static_assert(value >= NXS_COUNTER_WARPS, "a tile this large leaves too few stages");
+  static constexpr int value = fit < 2 ? 2 : fit > NXS_MAX_STAGES ? NXS_MAX_STAGES : fit;
 };
 
 // What a worker warp leaves behind for its range of the tile.
@@ -104,6 +101,7 @@ template <int TILE> struct __align__(128) StageBuf {
   uint32_t tailmask[TILE / 32]; // bit b: record 32*chunk + b is the last of its job
   RangeInfo range[kWorkerWarps];
   uint32_t range_off[kWorkerWarps]; // jobs ending before each range, tile-local
+  uint32_t part_total[kCounterWarps]; // jobs ending in each counter warp's part of the tile
   uint32_t tile_base;               // job rows before the tile
   uint32_t first_is_head;           // the tile's first record begins a job
   int32_t tile;                     // tile id, -1 = end of work
@@ -129,11 +127,10 @@ struct PendingTile {
 
 template <int STAGES> struct Ctl {
   uint64_t full[STAGES];       // tile landed              (producer -> workers)
+  uint64_t marked[STAGES];     // job boundaries marked    (counter warps -> the tile's owner among them)
   uint64_t base_ready[STAGES]; // first row index known    (counter warp -> workers)
   uint64_t p1done[STAGES];     // rows written             (workers -> summary warp)
   uint64_t freeb[STAGES];      // stage reusable           (summary warp -> producer)
-  uint32_t end_k;              // how many tiles this CTA claimed (set by the producer with the end marker)
-  uint32_t pad;
   PendingTile pending[kPendingSlots];
   // Tables of the classification pass.  Entries are pre-scaled to byte offsets so that an address is
   // one instruction: vt entry of a record = vt + lut[..] + lut2[..].
@@ -224,7 +221,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
 #ifdef NXS_TRACE
 // Debug build only: CTAs 0, 97 and 211 log pipeline events with the global timer.
 enum : uint32_t { EV_CLAIM = 1, EV_ISSUED, EV_COUNT_START, EV_COUNT_END, EV_LB_START, EV_LB_END, EV_P1_START,
-                  EV_P1_END, EV_SUM_START, EV_SUM_END, EV_LB_POLL, EV_SLB_END, EV_STEP };
+                  EV_P1_END, EV_SUM_START, EV_SUM_END, EV_LB_POLL, EV_SLB_END, EV_STEP, EV_W_IDLE, EV_W_BUSY, EV_C_MARK, EV_C_LB, EV_C_IDLE };
 __device__ __forceinline__ void trace_event(const ClassifyParams &p, uint32_t ev, uint32_t tile) {
   if (!p.trace || !(blockIdx.x == 0 || blockIdx.x == 97 || blockIdx.x == 211)) return;
   const unsigned long long i = atomicAdd(p.trace, 1ull);
@@ -232,8 +229,15 @@ __device__ __forceinline__ void trace_event(const ClassifyParams &p, uint32_t ev
   p.trace[1 + 2 * i] = global_timer_ns();
   p.trace[2 + 2 * i] = (unsigned long long)blockIdx.x << 40 | (unsigned long long)ev << 32 | tile;
 }
-#define NXS_TRACE_EVENT(p, ev, tile) trace_event(p, ev, tile)
+#ifdef NXS_TRACE_STATS // only the per-warp idle/busy totals (no per-tile events: they cost ~0.6 us each)
+#define NXS_TRACE_EVENT(p, ev, tile) ((void)0)
+#define NXS_TRACE_STAT(p, ev, v) trace_event(p, ev, v)
 #else
+#define NXS_TRACE_EVENT(p, ev, tile) trace_event(p, ev, tile)
+#define NXS_TRACE_STAT(p, ev, v) ((void)0)
+#endif
+#else
+#define NXS_TRACE_STAT(p, ev, v) ((void)0)
 #define NXS_TRACE_EVENT(p, ev, tile) ((void)0)
 #endif
 
@@ -282,28 +286,36 @@ __device__ __forceinline__ Summ shfl_summ(Summ s, int src) {
 // --------------------------------------------------------------------- producer
 template <int TILE, int STAGES>
 __device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl) {
-  uint32_t next = atomicAdd(p.counters, 1u);
   Watchdog wd;
+  // the first tiles of the CTA (one per stage when there is enough work) are claimed in one go
+  const uint32_t per_cta = (p.n_tiles + gridDim.x - 1) / gridDim.x;
+  const uint32_t n_first = per_cta < (uint32_t)STAGES ? per_cta : (uint32_t)STAGES;
+  const uint32_t first = atomicAdd(p.counters, n_first);
   for (uint32_t k = 0;; ++k) {
     const uint32_t s = k % STAGES, use = k / STAGES;
+    // A tile id is claimed only when its stage is about to be free: every later tile of the grid waits
+    // (in its look-back) for the count of this one, so an id must not be held while the ring is full.
+    // The claim is issued when the workers are done with the stage's previous tile, and its round trip
+    // overlaps the summary warp's last reads of the stage.
     if (use > 0) {
-      while (!mbar_try_wait(&ctl.freeb[s], (use - 1) & 1u, 20000u)) {
+      while (!mbar_try_wait(&ctl.p1done[s], (use - 1) & 1u, 20000u)) {
         aux_nap<NXS_PRODUCER_NS>();
         wd.tick(p.counters + 2);
       }
+    }
+    const uint32_t id = k < n_first ? first + k : atomicAdd(p.counters, 1u);
+    if (use > 0) {
+      while (!mbar_try_wait(&ctl.freeb[s], (use - 1) & 1u, 20000u)) wd.tick(p.counters + 2);
       wd.reset();
     }
     StageBuf<TILE> &sb = stages[s];
     uint64_t *bar = &ctl.full[s];
-    const uint32_t id = next;
     if (id >= p.n_tiles) {
       sb.tile = -1;
-      *reinterpret_cast<volatile uint32_t *>(&ctl.end_k) = k;
       mbar_arrive_n(bar, 2);
       break;
     }
     NXS_TRACE_EVENT(p, EV_CLAIM, id);
-    next = atomicAdd(p.counters, 1u); // consumed one iteration later: latency hidden
     sb.tile = (int32_t)id;
     const uint32_t start = id * TILE;
     if (p.n - start >= (uint32_t)TILE) {
@@ -329,22 +341,24 @@ __device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<
   }
 }
 
-// -------------------------------------------------------- job boundaries (counter warp)
-// Marks the job boundaries of a landed tile: the "last record of its job" bit masks, the
-// number of jobs ending before each worker range, whether the tile's first record begins a
-// job; returns the tile's job count (warp-uniform).  A ragged (last) tile is read from
-// global memory here and copied into the stage for the classification pass.
+// ------------------------------------------------------- job boundaries (counter warps)
+// Every counter warp marks one part of a landed tile (part q = worker ranges q*RPP ..): the
+// "last record of its job" bit masks, the number of jobs ending before each of its ranges
+// (relative to the part) and the part's job count; part 0 also notes whether the tile's first
+// record begins a job.  A ragged (last) tile is read from global memory here and copied into
+// the stage for the classification pass.
 template <int TILE>
-__device__ __forceinline__ uint32_t count_tile(const ClassifyParams &p, StageBuf<TILE> &sb, uint32_t tile,
-                                                uint32_t lane) {
-  constexpr uint32_t RANGE = TILE / kWorkerWarps, CPW = RANGE / 32;
+__device__ __forceinline__ void count_part(const ClassifyParams &p, StageBuf<TILE> &sb, uint32_t tile, uint32_t part,
+                                           uint32_t lane) {
+  static_assert(kWorkerWarps % kCounterWarps == 0, "the worker ranges are split evenly among the counter warps");
+  constexpr uint32_t RANGE = TILE / kWorkerWarps, CPW = RANGE / 32, RPP = kWorkerWarps / kCounterWarps;
   const uint32_t start = tile * TILE;
   const uint32_t cnt = min((uint32_t)TILE, p.n - start);
   uint32_t total = 0;
   if (cnt == (uint32_t)TILE) {
     const bool last_tile = start + cnt == p.n;
 #pragma unroll 1
-    for (uint32_t r = 0; r < (uint32_t)kWorkerWarps; ++r) {
+    for (uint32_t r = part * RPP; r < (part + 1) * RPP; ++r) {
       uint32_t jobs = 0;
 #pragma unroll
       for (uint32_t j = 0; j < CPW; ++j) {
@@ -358,9 +372,9 @@ __device__ __forceinline__ uint32_t count_tile(const ClassifyParams &p, StageBuf
       if (lane == 0) sb.range_off[r] = total;
       total += jobs;
     }
-    if (lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(sb.keyx[2] != sb.keyx[1]);
-  } else { // ragged last tile (once per launch): read from global memory, copied into the stage
-    for (uint32_t c = 0; c < (uint32_t)TILE / 32; ++c) {
+    if (part == 0 && lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(sb.keyx[2] != sb.keyx[1]);
+  } else { // ragged last tile (once per launch)
+    for (uint32_t c = part * RPP * CPW; c < (part + 1) * RPP * CPW; ++c) {
       const uint32_t i = c * 32 + lane;
       bool tail = false;
       if (i < cnt) {
@@ -379,9 +393,9 @@ __device__ __forceinline__ uint32_t count_tile(const ClassifyParams &p, StageBuf
       }
       total += __popc(T);
     }
-    if (lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(p.key[start] != p.key[start - 1]);
+    if (part == 0 && lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(p.key[start] != p.key[start - 1]);
   }
-  return total;
+  if (lane == 0) sb.part_total[part] = total;
 }
 
 // ----------------------------------------------------------------- counter warp
@@ -422,45 +436,66 @@ __device__ __forceinline__ bool count_lookback_poll(const ClassifyParams &p, Cou
   return false;
 }
 
-// Counter warp `which` handles the tiles k = which, which + kCounterWarps, ... of the CTA (k = order in
-// which the CTA claimed them), so that several look-backs are in flight per CTA: one look-back costs
-// a few L2 round trips, several times the time a tile may take at full speed.  Each warp is an event
-// loop: counting a freshly landed tile and publishing its count always comes before polling for an
-// older one, because every later tile of every CTA waits for that count.  (The ring depth is a
-// multiple of kCounterWarps: a stage's `full` barrier is only ever watched by one counter warp, in
-// phase order — a parity wait cannot tell a phase from the one two before it.)
+// The counter warps of a CTA share the marking of every tile (each takes a part, see count_part) and
+// take the tiles in turn for the rest: counter warp `which` OWNS the tiles k = which, which +
+// kCounterWarps, ... (k = order in which the CTA claimed them); the owner adds up the parts, publishes
+// the tile's job count and runs the look-back, so that several look-backs are in flight per CTA: one
+// look-back costs a few L2 round trips, more than the time a tile may take at full speed.  Each warp is
+// an event loop with this order of duties: mark a freshly landed tile, publish the count of an own
+// tile that is fully marked, poll for the oldest own tile — every later tile of every CTA waits for the
+// counts.  Every counter warp watches every use of every `full` barrier in order and arrives on
+// `marked` itself before it waits there, so no parity wait can mistake a phase for the one two before.
 template <int TILE, int STAGES>
 __device__ __forceinline__ void counter_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
                                              uint32_t which, uint32_t lane) {
-  uint32_t ka = which, kl = which; // next own tile to count / to look back for
-  bool end = false, lb_active = false;
+  constexpr uint32_t RPP = kWorkerWarps / kCounterWarps;
+  uint32_t km = 0;                 // next tile of the CTA to mark (all of them, in order)
+  uint32_t kf = which, kl = which; // next own tile to publish the count of / to look back for
+  uint32_t k_end = 0xFFFFFFFFu;    // index of the end marker, once seen
+  bool lb_active = false;
   CountLookback st{0, 0u};
   Watchdog wd;
   while (true) {
-    const uint32_t sa = ka % STAGES, para = (ka / STAGES) & 1u;
-    uint64_t *const arrival = &ctl.full[sa]; // the counter warp marks the job boundaries itself
-    if (!end && __all_sync(0xffffffffu, mbar_test_wait(arrival, para))) {
-      StageBuf<TILE> &sb = stages[sa];
+    const uint32_t sm = km % STAGES;
+    if (k_end == 0xFFFFFFFFu && __all_sync(0xffffffffu, mbar_test_wait(&ctl.full[sm], (km / STAGES) & 1u))) {
+      StageBuf<TILE> &sb = stages[sm];
       const int32_t t = sb.tile;
       if (t < 0) {
-        end = true;
+        k_end = km;
       } else {
-        const uint32_t tile = (uint32_t)t;
-        if (lane == 0) NXS_TRACE_EVENT(p, EV_COUNT_START, tile);
-        const uint32_t incl = count_tile<TILE>(p, sb, tile, lane);
-        if (lane == 0) {
-          sb.total = incl;
-          st_desc_word(&p.desc[tile].c, desc_c(incl, tile == 0 ? DESC_INC : DESC_AGG, p.gen));
-          if (p.n_tiles == 1) *p.n_jobs = incl;
-        }
+        if (lane == 0 && km % kCounterWarps == which) NXS_TRACE_EVENT(p, EV_COUNT_START, (uint32_t)t);
+        count_part<TILE>(p, sb, (uint32_t)t, which, lane);
         __syncwarp();
-        if (lane == 0) NXS_TRACE_EVENT(p, EV_COUNT_END, tile);
-        ka += kCounterWarps;
+        if (lane == 0) mbar_arrive(&ctl.marked[sm]);
+        ++km;
       }
       wd.reset();
       continue;
     }
-    if (kl < ka) { // look up the first row index of the oldest own tile (one round trip per poll)
+    if (kf < km && __all_sync(0xffffffffu, mbar_test_wait(&ctl.marked[kf % STAGES], (kf / STAGES) & 1u))) {
+      StageBuf<TILE> &sb = stages[kf % STAGES];
+      const uint32_t tile = (uint32_t)sb.tile;
+      // job rows before each part, then before each range, of the tile
+      uint32_t before = 0, total = 0;
+#pragma unroll
+      for (uint32_t q = 0; q < (uint32_t)kCounterWarps; ++q) {
+        const uint32_t c = sb.part_total[q];
+        if (q < lane / RPP) before += c;
+        total += c;
+      }
+      if (lane < (uint32_t)kWorkerWarps && before) sb.range_off[lane] += before;
+      if (lane == 0) {
+        sb.total = total;
+        st_desc_word(&p.desc[tile].c, desc_c(total, tile == 0 ? DESC_INC : DESC_AGG, p.gen));
+        if (p.n_tiles == 1) *p.n_jobs = total;
+        NXS_TRACE_EVENT(p, EV_COUNT_END, tile);
+      }
+      __syncwarp();
+      kf += kCounterWarps;
+      wd.reset();
+      continue;
+    }
+    if (kl < kf) { // look up the first row index of the oldest own tile (one round trip per poll)
       const uint32_t sl = kl % STAGES;
       StageBuf<TILE> &sb = stages[sl];
       const uint32_t tile = (uint32_t)sb.tile;
@@ -489,13 +524,15 @@ __device__ __forceinline__ void counter_loop(const ClassifyParams &p, StageBuf<T
       wd.tick(p.counters + 2);
       continue;
     }
-    if (end) { // this warp met the end marker: wake the workers
-      if (lane == 0) mbar_arrive(&ctl.base_ready[sa]);
+    if (k_end != 0xFFFFFFFFu && kf >= k_end) { // every own tile is done (kl == kf here)
+      // the end marker takes a turn like a tile: its owner wakes the workers
+      if (k_end % kCounterWarps == which && lane == 0) mbar_arrive(&ctl.base_ready[k_end % STAGES]);
       break;
     }
-    // the CTA's last tile may belong to another counter warp: stop once the claim count is known
-    if (*reinterpret_cast<volatile uint32_t *>(&ctl.end_k) < ka) break;
-    if (!__all_sync(0xffffffffu, mbar_try_wait(arrival, para, 2000u))) aux_nap<NXS_COUNTER_NS>();
+    // nothing to do: wait for the next tile to land, or for the partners to finish marking an own one
+    if (k_end == 0xFFFFFFFFu && kf >= km) {
+      if (!__all_sync(0xffffffffu, mbar_try_wait(&ctl.full[sm], (km / STAGES) & 1u, 2000u))) aux_nap<NXS_COUNTER_NS>();
+    }
     wd.tick(p.counters + 2);
   }
 }
@@ -614,14 +651,24 @@ __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TI
   uint32_t s = 0, par = 0; // next tile to classify: stage, parity
   const uint32_t base_addr = smem_u32_pinned(&ctl.base_ready[0]), done_addr = smem_u32_pinned(&ctl.p1done[0]);
   Watchdog wd;
+#ifdef NXS_TRACE_STATS
+  uint64_t st_idle = 0, st_busy = 0;
+#endif
   while (true) {
     // Classify when the tile's first row index is known.  Until then an idle warp sleeps off the issue
     // slots in a loop kept as short as possible (a barrier test, a nap): every instruction an idle warp
     // issues is taken from a busy one.
+#ifdef NXS_TRACE_STATS
+    const uint64_t t_a = global_timer_ns();
+#endif
     while (!__all_sync(0xffffffffu, mbar_test_wait_a(base_addr + 8u * s, par))) {
       __nanosleep(NXS_IDLE_NS);
       wd.tick(p.counters + 2);
     }
+#ifdef NXS_TRACE_STATS
+    const uint64_t t_b = global_timer_ns();
+    st_idle += t_b - t_a;
+#endif
     wd.reset();
     StageBuf<TILE> &sb = stages[s];
     const int32_t t = sb.tile;
@@ -634,6 +681,13 @@ __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TI
       if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_END, (uint32_t)t);
     }
     __syncwarp();
+#ifdef NXS_TRACE_STATS
+    st_busy += global_timer_ns() - t_b;
+    if (t < 0 && lane == 0) {
+      NXS_TRACE_STAT(p, EV_W_IDLE, (uint32_t)(st_idle >> 4) | warp << 28);
+      NXS_TRACE_STAT(p, EV_W_BUSY, (uint32_t)(st_busy >> 4) | warp << 28);
+    }
+#endif
     if (lane == 0) mbar_arrive_a(done_addr + 8u * s);
     if (t < 0) break;
     if (++s == STAGES) s = 0, par ^= 1u;
@@ -814,7 +868,7 @@ __device__ __forceinline__ void summary_loop(const ClassifyParams &p, StageBuf<T
 }
 
 #ifndef NXS_MAXNREG
-#define NXS_MAXNREG 80
+#define NXS_MAXNREG 72 /* 448 threads x 72 registers x 2 CTAs fit the register file */
 #endif
 template <int TILE>
 __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__ ClassifyParams p) {
@@ -829,6 +883,7 @@ __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&ctl.full[s], 2);
+      mbar_init(&ctl.marked[s], kCounterWarps);
       mbar_init(&ctl.base_ready[s], 1);
       mbar_init(&ctl.p1done[s], kWorkerWarps);
       mbar_init(&ctl.freeb[s], 1);
@@ -842,7 +897,6 @@ __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__
     ctl.lut2[e] = (uint8_t)(32u * ((fl & 3u) != 3u ? 0u : !(fl & NXS_FLAG_CHECKPOINT) ? 1u : fin ? 2u : 3u) + 128u * fin);
   }
   if (tid < 8) ctl.code[tid] = p.code[tid];
-  if (tid == 0) ctl.end_k = 0xFFFFFFFFu;
   if (tid >= 128 && tid < 192) {
     const uint32_t e = tid - 128, g = (e >> 3) & 3u, arm = e & 7u;
     const uint32_t code = p.code[arm], a = code & 7u, msg = code >> 9;

@@ -47,15 +47,21 @@ def main():
     per = {}
     polls = {}
     steps = {}
+    stats = {}
     for t, w in ev:
         cta, e, tile = int(w) >> 40, (int(w) >> 32) & 255, int(w) & 0xFFFFFFFF
         if e == 11:
             polls[(cta, tile)] = polls.get((cta, tile), 0) + 1
+        elif e in (14, 15):  # NXS_TRACE_STATS build: per-worker-warp idle / busy totals (ns / 16)
+            stats.setdefault(cta, {}).setdefault(tile >> 28, {})["idle" if e == 14 else "busy"] = (tile & 0xFFFFFFF) * 16
         elif e == 13:  # NXS_TRACE_STEPS build: end of 32-record step j of warp 0
             steps.setdefault((cta, tile & 0xFFFFFF), {})[tile >> 24] = int(t) - t0
         else:
             per.setdefault((cta, tile), {})[EV[e]] = int(t) - t0
     print(f"{cnt} events, span {(int(ev[:, 0].max()) - t0) / 1e3:.1f} us")
+    for cta, ws in sorted(stats.items()):
+        print(f"--- CTA {cta}: worker warps, us waiting for a tile / us classifying: " +
+              "  ".join(f"w{w}: {v.get('idle', 0) / 1e3:.0f}/{v.get('busy', 0) / 1e3:.0f}" for w, v in sorted(ws.items())))
     for cta in sorted({k[0] for k in per}):
         tiles = sorted(k[1] for k in per if k[0] == cta)
         print(f"--- CTA {cta}: {len(tiles)} tiles; claim in us from kernel start; durations in ns")
