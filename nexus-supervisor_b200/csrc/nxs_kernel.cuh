@@ -5,14 +5,15 @@
 // the records of each job into one row.  Each CTA is a warp-specialised pipeline
 // over a ring of shared-memory stages, driven by mbarriers only:
 //
-//   producer warp   claims tile ids from a global counter and streams the five
-//                   input columns of a tile into a stage with 1-D bulk async
-//                   copies (TMA engine, SASS UBLKCP)
-//   counter warps   (two, taking the CTA's tiles in turn) as soon as a tile has landed:
-//                   compare the adjacent job keys, leave the "last record of a job" bit
-//                   masks and the jobs-per-range offsets in the stage, publish the tile's
-//                   JOB COUNT, poll predecessor tiles (decoupled look-back on counts only)
-//                   for the index of the tile's first job row and release the workers
+//   producer warp   claims a tile id from a global counter when a stage is about to be
+//                   free and streams the five input columns of the tile into the stage
+//                   with 1-D bulk async copies (TMA engine, SASS UBLKCP)
+//   counter warps   (four) as soon as a tile has landed each marks a quarter of it:
+//                   compares the adjacent job keys, leaves the "last record of a job"
+//                   bit masks and the jobs-per-range offsets in the stage; the tile's
+//                   owner among them (they take the tiles in turn) publishes the tile's
+//                   JOB COUNT, polls predecessor tiles (decoupled look-back on counts
+//                   only) for the index of the tile's first job row and releases the workers
 //   worker warps    each warp owns a contiguous range of the tile and walks it 32
 //                   records at a time, lane per record: table lookups -> packed
 //                   verdict -> global; warp ballots -> bit masks in registers; the
