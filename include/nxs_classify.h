@@ -201,7 +201,7 @@ uint64_t nxs_launch_count(const nxs_ctx *ctx);
  * it, or a latency-critical loop that cannot afford the device-wide stall a
  * cudaMalloc/cudaFree can cause.  It needs no nxs_ctx and calls no allocating
  * routine: the tile descriptors and counters the kernel uses as scratch live in
- * a static __device__ array inside the library (about 128 KiB on every GPU that
+ * a static __device__ array inside the library (about 32 KiB on every GPU that
  * loads the library, until the process exits), which bounds a call to
  * NXS_NOALLOC_MAX_RECORDS records; larger batches are refused with
  * NXS_ERR_NOALLOC_LIMIT and nothing is launched.

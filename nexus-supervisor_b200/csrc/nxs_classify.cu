@@ -439,8 +439,8 @@ void nxs_free_host(void *p) {
 // pool owns the HBM budget, or a cudaMalloc/cudaFree stall is unacceptable on
 // their hot loop).  The kernel's scratch — one 16-byte descriptor per tile plus
 // the counters — lives in this file-scope __device__ array instead of a
-// cudaMalloc'ed buffer: 2048-record tiles, so NXS_NOALLOC_MAX_RECORDS = 2^24
-// records need 8192 descriptors (128 KiB) + 256 bytes for the counters.  Every
+// cudaMalloc'ed buffer: 8192-record tiles, so NXS_NOALLOC_MAX_RECORDS = 2^24
+// records need 2048 descriptors (32 KiB) + 256 bytes for the counters.  Every
 // GPU that loads the library carries the array until the process exits.
 //
 // `g_noalloc_scratch` as written in host code is only a host-side handle for the

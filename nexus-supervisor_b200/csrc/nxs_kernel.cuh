@@ -38,7 +38,7 @@
 namespace nxs {
 
 #ifndef NXS_WORKERS
-#define NXS_WORKERS 8
+#define NXS_WORKERS 16
 #endif
 constexpr int kWorkerWarps = NXS_WORKERS;
 constexpr int kWorkers = kWorkerWarps * 32;
@@ -46,7 +46,7 @@ constexpr int kProducerWarp = kWorkerWarps;
 constexpr int kSummaryWarp = kWorkerWarps + 1;
 constexpr int kCounterWarp0 = kWorkerWarps + 2; // first of kCounterWarps counter warps
 #ifndef NXS_COUNTER_WARPS
-#define NXS_COUNTER_WARPS 4
+#define NXS_COUNTER_WARPS 8
 #endif
 constexpr int kCounterWarps = NXS_COUNTER_WARPS; // tile k of a CTA is counted and looked up by counter warp k % kCounterWarps
 constexpr int kThreads = kWorkers + 64 + 32 * kCounterWarps;
@@ -56,23 +56,23 @@ constexpr uint64_t kWatchdogNs = 8000000000ull; // a stuck wait traps instead of
 // The three tile sizes built into the library (NXS_TILE selects one at run time); each must
 // be a multiple of 32 * NXS_WORKERS.
 #ifndef NXS_TILE_S
-#define NXS_TILE_S 1024
+#define NXS_TILE_S 2048
 #endif
 #ifndef NXS_TILE_M
-#define NXS_TILE_M 2048
+#define NXS_TILE_M 4096
 #endif
 #ifndef NXS_TILE_L
-#define NXS_TILE_L 4096
+#define NXS_TILE_L 8192
 #endif
 #ifndef NXS_TILE_DEFAULT
-#define NXS_TILE_DEFAULT NXS_TILE_M
+#define NXS_TILE_DEFAULT NXS_TILE_L
 #endif
-// Ring depth: as many stages as fit in half an SM's shared memory (two CTAs per SM), 2..NXS_MAX_STAGES.
+// Ring depth: as many stages as fit in the shared-memory budget of a CTA, 2..NXS_MAX_STAGES.
 #ifndef NXS_MAX_STAGES
-#define NXS_MAX_STAGES 4
+#define NXS_MAX_STAGES 8
 #endif
 #ifndef NXS_SMEM_BUDGET_KB
-#define NXS_SMEM_BUDGET_KB 110
+#define NXS_SMEM_BUDGET_KB 222 /* one CTA per SM */
 #endif
 constexpr int kStageBudgetBytes = NXS_SMEM_BUDGET_KB * 1024;
 template <int TILE> struct StagesFor {
@@ -200,7 +200,7 @@ template <int TILE> constexpr size_t classify_smem_bytes() {
 #if defined(__CUDACC__)
 
 #ifndef NXS_IDLE_NS
-#define NXS_IDLE_NS 500
+#define NXS_IDLE_NS 200
 #endif
 #ifndef NXS_CLASSIFY_UNROLL
 #define NXS_CLASSIFY_UNROLL 2
@@ -869,7 +869,7 @@ __device__ __forceinline__ void summary_loop(const ClassifyParams &p, StageBuf<T
 }
 
 #ifndef NXS_MAXNREG
-#define NXS_MAXNREG 72 /* 448 threads x 72 registers x 2 CTAs fit the register file */
+#define NXS_MAXNREG 72 /* 832 threads x 72 registers fit the register file */
 #endif
 template <int TILE>
 __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__ ClassifyParams p) {

@@ -1,7 +1,7 @@
 #!/bin/bash
 # Run on the B200 box via gpurun: smoke, GPU parity tests, bench, then the ncu launch list and one
 # full capture of the classification kernel.  Everything is logged under gpurun_out/.
-# Env: SKIP_TESTS=1, SKIP_NCU=1, TILES="1024 2048 4096" (extra kernel-only bench lines per tile variant)
+# Env: SKIP_TESTS=1, SKIP_NCU=1, TILES="2048 4096 8192" (extra kernel-only bench lines per tile variant)
 set -u
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/gpu.txt 2>&1

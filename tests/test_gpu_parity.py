@@ -50,7 +50,8 @@ def test_exhaustive_domain(fm):
             util.assert_same(*c.classify(cols), *cpu_oracle.classify(cols, fm), f"fm={fm:#x} per_job={per_job}")
 
 
-@pytest.mark.parametrize("n", [1, 2, 31, 32, 33, 2047, 2048, 2049, 4095, 4097, 6144, 100_003, 1_000_000])
+@pytest.mark.parametrize("n", [1, 2, 31, 32, 33, 2047, 2048, 2049, 4095, 4097, 6144, 8191, 8192, 8193, 16385, 24576,
+                               100_003, 1_000_000])
 def test_ragged_sizes(clf, n):
     rng = np.random.default_rng(n)
     cols = util.random_cols(rng, n, 5)
@@ -85,15 +86,15 @@ def test_single_job_batch(clf):
             util.assert_same(verdict, rows, *cpu_oracle.classify(cols, fm), f"single job fm={fm:#x}")
 
 
-@pytest.mark.parametrize("tile", ["1024", "2048", "4096"])
+@pytest.mark.parametrize("tile", ["2048", "4096", "8192"])
 def test_tile_variants_and_context_reuse(tile, monkeypatch):
     monkeypatch.setenv("NXS_TILE", tile)
     rng = np.random.default_rng(int(tile))
     with nx.Classifier(device=0, max_records=2_000_000) as c:
-        for n, max_len in ((1_500_000, 6), (5, 2), (777_777, 3000), (2_000_000, 2), (4096, 1)):
+        for n, max_len in ((1_500_000, 6), (5, 2), (777_777, 3000), (2_000_000, 2), (4096, 1), (8192, 1)):
             cols = util.random_cols(rng, n, max_len)
             util.assert_same(*c.classify(cols), *cpu_oracle.classify(cols), f"tile={tile} n={n}")
-        assert c.launches == 5
+        assert c.launches == 6
 
 
 def test_host_path_slices_on_job_boundaries():
