@@ -8,7 +8,7 @@
 //   producer warp   claims a tile id from a global counter when a stage is about to be
 //                   free and streams the five input columns of the tile into the stage
 //                   with 1-D bulk async copies (TMA engine, SASS UBLKCP)
-//   counter warps   (four) as soon as a tile has landed each marks a quarter of it:
+//   counter warps   (eight) as soon as a tile has landed each marks an eighth of it:
 //                   compares the adjacent job keys, leaves the "last record of a job"
 //                   bit masks and the jobs-per-range offsets in the stage; the tile's
 //                   owner among them (they take the tiles in turn) publishes the tile's
@@ -405,7 +405,7 @@ struct CountLookback {
   uint32_t excl; // job rows counted so far
 };
 #ifndef NXS_COUNT_WINDOWS
-#define NXS_COUNT_WINDOWS 2
+#define NXS_COUNT_WINDOWS 1 /* 8192-record tiles: 32 predecessors per poll reach far enough */
 #endif
 constexpr int kCountWindows = NXS_COUNT_WINDOWS;
 // One non-blocking step of the count look-back: kCountWindows x 32 predecessor count
