@@ -203,7 +203,7 @@ template <int TILE> constexpr size_t classify_smem_bytes() {
 #define NXS_IDLE_NS 200
 #endif
 #ifndef NXS_CLASSIFY_UNROLL
-#define NXS_CLASSIFY_UNROLL 2
+#define NXS_CLASSIFY_UNROLL 4 /* of the 16 steps of a range; 2 measured 1 % slower, 1 another 1 % */
 #endif
 constexpr int kClassifyUnroll = NXS_CLASSIFY_UNROLL;
 
