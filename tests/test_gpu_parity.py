@@ -97,6 +97,22 @@ def test_tile_variants_and_context_reuse(tile, monkeypatch):
         assert c.launches == 6
 
 
+def test_soak_many_launches_random_sizes(clf):
+    """Many launches on one context with sizes around every hand-over of the pipeline (one tile, a few tiles,
+    one tile per CTA, a little more than one per CTA and stage), long and short jobs: a rare ordering
+    problem between the producer, the counter warps and the workers shows up as a wrong row or a trap."""
+    rng = np.random.default_rng(20261107)
+    sizes = [1, 8191, 8192, 8193, 16384, 16385]
+    sizes += [int(x) for x in rng.integers(1, 60_000, 40)]
+    sizes += [int(x) for x in rng.integers(148 * 8192 - 9000, 148 * 8192 + 9000, 10)]
+    sizes += [int(x) for x in rng.integers(2 * 148 * 8192 - 9000, 2 * 148 * 8192 + 20_000, 10)]
+    sizes += [int(x) for x in rng.integers(100_000, 5_000_000, 40)]
+    for k, n in enumerate(sizes):
+        max_len = (1, 2, 5, 40, 5000)[k % 5]
+        cols = util.random_cols(rng, n, max_len)
+        util.assert_same(*clf.classify(cols), *cpu_oracle.classify(cols), f"soak launch {k} n={n} max_len={max_len}")
+
+
 def test_host_path_slices_on_job_boundaries():
     """The host-pointer entry point processes large batches in ~8M-record slices (upload, classify and
     download overlapped); slices are cut on job boundaries and winner indices stay batch-relative."""
