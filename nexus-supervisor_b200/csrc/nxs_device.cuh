@@ -187,7 +187,7 @@ constexpr uint32_t kCodeRunning = NXS_ACTION_RUNNING | NXS_STAGE_RUNNING << 3; /
 // --------------------------------------------------------------- fold algebra
 // Summary of a run of consecutive records of ONE job, valid under the premise
 // "the row was not finished when the run began".  (If it was, nothing applies
-// and every handled record is a skip — summ_resolve handles that with F_FIN0.)
+// and every handled record is a skip: the job's anchor then carries a stop, see summ_anchor.)
 // The low 16 bits ARE the packed verdict fields, so closing a job is a mask.
 struct Summ {
   uint32_t win_idx; // record index of the winner (if F_HAS_WIN)
@@ -201,15 +201,22 @@ enum : uint32_t {
   F_SKIP = 1u << 14,      // some handled record came after the stop (verdict.skip_finished)
   F_ERR = 1u << 15,       // some record had no checkpoint (verdict.err = 1)
   F_STOPPED = 1u << 16,   // an applied record moved the row to a finished stage
-  F_FIN0 = 1u << 17,      // the row was already finished at the job's first record (valid iff anchored)
+  F_FIN0 = 1u << 17,      // the row was already finished at the job's first record (informational: it comes with F_STOPPED)
   F_ANCHORED = 1u << 18,  // the run starts at the job's first record (look-back stops here)
   F_BITS = 19
 };
 
 __host__ __device__ __forceinline__ Summ summ_identity() { return Summ{0u, 0u}; }
 // A run that begins at the job's first record; fin0 = IsFinished() of the row it found (:276).
+// A finished row is a stop before the job's first record: nothing after it applies, every handled
+// record is a skip (:276-279) — which is exactly what summ_combine does to the right of a stop.
 __host__ __device__ __forceinline__ Summ summ_anchor(bool fin0) {
-  return Summ{0u, F_ANCHORED | (fin0 ? F_FIN0 : 0u)};
+  return Summ{0u, F_ANCHORED | (fin0 ? (F_FIN0 | F_STOPPED) : 0u)};
+}
+// anchor(fin0) combined with a piece computed under the premise, on the flags alone
+__host__ __device__ __forceinline__ uint32_t summ_anchor_flags(uint32_t piece_f, uint32_t fin0_bit) {
+  if (fin0_bit) piece_f = (piece_f & F_ERR) | F_STOPPED | ((piece_f & F_HAS_APP) << 1); // F_HAS_APP -> F_SKIP
+  return piece_f | F_ANCHORED | fin0_bit;
 }
 __host__ __device__ __forceinline__ uint64_t summ_pack(Summ s) {
   return (uint64_t)s.f << 32 | s.win_idx;
@@ -294,12 +301,10 @@ __host__ __device__ __forceinline__ Summ summ_piece(uint32_t he, uint32_t term, 
   return Summ{(f & F_HAS_WIN) ? global_base + base + wp : 0u, summ_piece_finish(f, cw, liw)};
 }
 
-// Close a job: apply the premise check and emit (verdict, winner_idx).
+// Close a job (its summary must be anchored): emit (verdict, winner_idx).
 __host__ __device__ __forceinline__ void summ_resolve(Summ s, uint32_t &verdict, uint32_t &winner) {
-  const bool fin0 = (s.f & F_FIN0) != 0;
-  const uint32_t v = fin0 ? (((s.f & F_HAS_APP) ? F_SKIP : 0u) | (s.f & F_ERR)) : (s.f & 0xFFFFu);
-  verdict = v | (s.f & F_ERR) >> 3; // a missing checkpoint also deletes the job (:268)
-  winner = (!fin0 && (s.f & F_HAS_WIN)) ? s.win_idx : NXS_NO_WINNER;
+  verdict = (s.f & 0xFFFFu) | (s.f & F_ERR) >> 3; // a missing checkpoint also deletes the job (:268)
+  winner = (s.f & F_HAS_WIN) ? s.win_idx : NXS_NO_WINNER;
 }
 
 } // namespace nxs

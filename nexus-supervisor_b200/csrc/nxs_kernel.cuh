@@ -616,7 +616,7 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
     if (tms) f |= F_STOPPED;
     if (hes & ~upto) f |= F_SKIP;
     Summ S{gidx + wp, f};
-    if (h_in) S.f |= F_ANCHORED | fin_head; // the job begins in this chunk
+    if (h_in) S.f = summ_anchor_flags(S.f, fin_head); // the job begins in this chunk
     else S = summ_combine(ctx, S);          // it continues the job left open before the chunk
 
     if (T & lanebit) { // this record ends a job: close it and store its row
