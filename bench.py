@@ -326,7 +326,7 @@ def main():
                    "seed": hex(nx.DEFAULT_SEED)},
         "e2e": e2e, "gpu_launches": int(gpu_launches), "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": "nxs::classify_kernel<%s>" % os.environ.get("NXS_TILE", "8192"), "kernel_ms": k_ms,
+                     "traffic": None, "kernel": "nxs::classify_kernel<%s>" % (os.environ.get("NXS_TILE") or (2048 if n <= 300_000 else 4096 if n <= (64 << 20) else 8192)), "kernel_ms": k_ms,
                      "algorithmic_bytes_per_launch": algo_bytes,
                      "bytes_model": "17 B/record (13 read + 4 verdict) + 16 B/job row",
                      "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / 8000.0},

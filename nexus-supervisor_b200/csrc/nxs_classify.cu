@@ -19,8 +19,8 @@ struct nxs_ctx {
   uint64_t max_records = 0;
   uint32_t finished_mask = 0;
   uint32_t term_mask = 0;
-  int tile = NXS_TILE_DEFAULT; // records per tile (kernel variant)
-  int ctas_per_sm = 1;    // resident CTAs of the chosen variant
+  int tile = 0;           // records per tile forced with NXS_TILE; 0 = chosen per launch from the batch size
+  int ctas_per_sm = 1;    // resident CTAs (the same for the three tile sizes: the ring fills the shared memory)
   uint32_t max_tiles = 0;
   TileDesc *desc = nullptr;
   uint32_t *counters = nullptr;
@@ -81,6 +81,16 @@ template <int TILE> int launch_variant(nxs_ctx *ctx, const ClassifyParams &p, ui
   return NXS_OK;
 }
 
+// Tile size for a batch of n records when NXS_TILE does not force one.  Measured on a B200
+// (scripts/small_batch.py, us per launch, 2048 / 4096 / 8192-record tiles): 2e5 records 10.5 / 15.7 /
+// 20.7, 4e6 68.6 / 38.6 / 43.5, 4e7 296 / 256 / 262, 6e7 423 / 369 / 372, 1e8 733 / 617 / 589: small
+// tiles spread a small batch over more SMs, large tiles mean fewer look-backs and hand-overs.
+int tile_for_batch(uint64_t n) {
+  if (n <= 300000u) return NXS_TILE_S;
+  if (n <= (64u << 20)) return NXS_TILE_M;
+  return NXS_TILE_L;
+}
+
 bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 } // namespace
@@ -134,18 +144,21 @@ int nxs_create(int device, uint64_t max_records, uint16_t finished_mask, nxs_ctx
   if (prop.major < 10) return bail(NXS_ERR_NO_DEVICE); // sm_100a code only
   ctx->num_sms = prop.multiProcessorCount;
   const char *tile_env = getenv("NXS_TILE");
-  ctx->tile = tile_env ? atoi(tile_env) : NXS_TILE_DEFAULT;
-  if (ctx->tile == NXS_TILE_S) rc = configure_variant<NXS_TILE_S>(ctx);
-  else if (ctx->tile == NXS_TILE_M) rc = configure_variant<NXS_TILE_M>(ctx);
-  else if (ctx->tile == NXS_TILE_L) rc = configure_variant<NXS_TILE_L>(ctx);
-  else rc = NXS_ERR_ARG;
+  ctx->tile = tile_env ? atoi(tile_env) : 0;
+  if (ctx->tile != 0 && ctx->tile != NXS_TILE_S && ctx->tile != NXS_TILE_M && ctx->tile != NXS_TILE_L) return bail(NXS_ERR_ARG);
+  rc = configure_variant<NXS_TILE_S>(ctx);
+  int occ_min = ctx->ctas_per_sm;
+  if (rc == NXS_OK) rc = configure_variant<NXS_TILE_M>(ctx);
+  occ_min = ctx->ctas_per_sm < occ_min ? ctx->ctas_per_sm : occ_min;
+  if (rc == NXS_OK) rc = configure_variant<NXS_TILE_L>(ctx);
+  ctx->ctas_per_sm = ctx->ctas_per_sm < occ_min ? ctx->ctas_per_sm : occ_min;
   if (rc != NXS_OK) return bail(rc);
   if (getenv("NXS_VERBOSE"))
-    fprintf(stderr, "nxs: device %d, %d SMs, tile %d records, %d resident CTAs/SM x %d threads\n", device,
-            ctx->num_sms, ctx->tile, ctx->ctas_per_sm, kThreads);
+    fprintf(stderr, "nxs: device %d, %d SMs, tile %d records (0 = by batch size), %d resident CTAs/SM x %d threads\n",
+            device, ctx->num_sms, ctx->tile, ctx->ctas_per_sm, kThreads);
   if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) return bail(NXS_ERR_CUDA);
   ctx->own_stream = true;
-  ctx->max_tiles = (uint32_t)((max_records + ctx->tile - 1) / ctx->tile);
+  ctx->max_tiles = (uint32_t)((max_records + NXS_TILE_S - 1) / NXS_TILE_S); // descriptors for the smallest tile
   if (cudaMalloc(&ctx->desc, sizeof(TileDesc) * (size_t)ctx->max_tiles) != cudaSuccess) return bail(NXS_ERR_NOMEM);
   if (cudaMalloc(&ctx->counters, 64) != cudaSuccess) return bail(NXS_ERR_NOMEM);
   if (cudaMemset(ctx->desc, 0, sizeof(TileDesc) * (size_t)ctx->max_tiles) != cudaSuccess) return bail(NXS_ERR_CUDA);
@@ -245,7 +258,8 @@ static int launch_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out
   p.desc = ctx->desc;
   p.counters = ctx->counters;
   p.n = (uint32_t)in->n;
-  p.n_tiles = (uint32_t)((in->n + ctx->tile - 1) / ctx->tile);
+  const int tile = ctx->tile ? ctx->tile : tile_for_batch(in->n);
+  p.n_tiles = (uint32_t)((in->n + tile - 1) / tile);
   p.record_base = record_base;
   p.finished_mask = ctx->finished_mask;
   p.term_mask = ctx->term_mask;
@@ -261,8 +275,8 @@ static int launch_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out
   const uint32_t max_grid = (uint32_t)(ctx->num_sms * ctx->ctas_per_sm);
   const uint32_t grid = p.n_tiles < max_grid ? p.n_tiles : max_grid;
   int rc;
-  if (ctx->tile == NXS_TILE_S) rc = launch_variant<NXS_TILE_S>(ctx, p, grid);
-  else if (ctx->tile == NXS_TILE_M) rc = launch_variant<NXS_TILE_M>(ctx, p, grid);
+  if (tile == NXS_TILE_S) rc = launch_variant<NXS_TILE_S>(ctx, p, grid);
+  else if (tile == NXS_TILE_M) rc = launch_variant<NXS_TILE_M>(ctx, p, grid);
   else rc = launch_variant<NXS_TILE_L>(ctx, p, grid);
   if (rc == NXS_OK) ctx->launches += 1;
   return rc;
