@@ -127,7 +127,8 @@ struct PendingTile {
 };
 
 template <int STAGES> struct Ctl {
-  uint64_t full[STAGES];       // tile landed              (producer -> workers)
+  uint64_t full[STAGES];       // the tile's keys landed    (producer -> counter warps)
+  uint64_t cols[STAGES];       // its other columns landed  (producer -> workers)
   uint64_t marked[STAGES];     // job boundaries marked    (counter warps -> the tile's owner among them)
   uint64_t base_ready[STAGES]; // first row index known    (counter warp -> workers)
   uint64_t p1done[STAGES];     // rows written             (workers -> summary warp)
@@ -314,24 +315,29 @@ __device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<
     if (id >= p.n_tiles) {
       sb.tile = -1;
       mbar_arrive_n(bar, 2);
+      mbar_arrive(&ctl.cols[s]);
       break;
     }
     NXS_TRACE_EVENT(p, EV_CLAIM, id);
     sb.tile = (int32_t)id;
     const uint32_t start = id * TILE;
     if (p.n - start >= (uint32_t)TILE) {
-      mbar_arrive_expect_tx(bar, 13u * TILE);
+      // the keys first, on their own barrier: marking the job boundaries needs nothing else
+      mbar_arrive_expect_tx(bar, 8u * TILE);
       bulk_g2s(&sb.keyx[2], p.key + start, 8u * TILE, bar);
-      bulk_g2s(sb.reason, p.reason + start, 2u * TILE, bar);
-      bulk_g2s(sb.kind, p.kind + start, TILE, bar);
-      bulk_g2s(sb.flags, p.flags + start, TILE, bar);
-      bulk_g2s(sb.stage, p.stage + start, TILE, bar);
       if (start > 0) cp_async_8(&sb.keyx[1], p.key + start - 1);
       if (start + TILE < p.n) cp_async_8(&sb.keyx[2 + TILE], p.key + start + TILE);
       mbar_arrive_after_cp_async(bar);
+      uint64_t *cbar = &ctl.cols[s];
+      mbar_arrive_expect_tx(cbar, 5u * TILE);
+      bulk_g2s(sb.reason, p.reason + start, 2u * TILE, cbar);
+      bulk_g2s(sb.kind, p.kind + start, TILE, cbar);
+      bulk_g2s(sb.flags, p.flags + start, TILE, cbar);
+      bulk_g2s(sb.stage, p.stage + start, TILE, cbar);
       NXS_TRACE_EVENT(p, EV_ISSUED, id);
     } else {
-      mbar_arrive_n(bar, 2); // ragged last tile: the workers load it themselves
+      mbar_arrive_n(bar, 2); // ragged last tile: the counter warps load it themselves
+      mbar_arrive(&ctl.cols[s]);
     }
   }
   // leave the counters zero for the next launch: the last CTA to stop claiming resets them
@@ -651,6 +657,7 @@ __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TI
                                             uint32_t warp, uint32_t lane) {
   uint32_t s = 0, par = 0; // next tile to classify: stage, parity
   const uint32_t base_addr = smem_u32_pinned(&ctl.base_ready[0]), done_addr = smem_u32_pinned(&ctl.p1done[0]);
+  const uint32_t cols_addr = smem_u32_pinned(&ctl.cols[0]);
   Watchdog wd;
 #ifdef NXS_TRACE_STATS
   uint64_t st_idle = 0, st_busy = 0;
@@ -670,6 +677,8 @@ __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TI
     const uint64_t t_b = global_timer_ns();
     st_idle += t_b - t_a;
 #endif
+    // (the other columns landed long ago: they were issued with the keys, and marking and the look-back came between)
+    while (!__all_sync(0xffffffffu, mbar_test_wait_a(cols_addr + 8u * s, par))) wd.tick(p.counters + 2);
     wd.reset();
     StageBuf<TILE> &sb = stages[s];
     const int32_t t = sb.tile;
@@ -884,6 +893,7 @@ __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&ctl.full[s], 2);
+      mbar_init(&ctl.cols[s], 1);
       mbar_init(&ctl.marked[s], kCounterWarps);
       mbar_init(&ctl.base_ready[s], 1);
       mbar_init(&ctl.p1done[s], kWorkerWarps);
