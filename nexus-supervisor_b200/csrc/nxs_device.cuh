@@ -301,6 +301,34 @@ __host__ __device__ __forceinline__ Summ summ_piece(uint32_t he, uint32_t term, 
   return Summ{(f & F_HAS_WIN) ? global_base + base + wp : 0u, summ_piece_finish(f, cw, liw)};
 }
 
+// ------------------------------------------------------------ one lane per job
+// The job pass of the kernel gives every run of records (a job, or the part of a job that lies in a
+// worker's range) to ONE lane.  The lane cuts the run's bits out of the per-chunk ballot words and
+// summarises them here.  All masks are already restricted to the run (bit 0 = its first record).
+//   hes: handled & checkpoint exists; tms: ... & the action's stage is finished; fl: failure action
+//   (need not be restricted); er: handled & no checkpoint.
+//   stop0: the run starts at the job's first record and IsFinished() held for the row it found
+//   (:276) — the anchor's stop: nothing applies and every handled record is a skip.
+// Returns the flags except the winner's code bits; wm = the applied failure records (winner = its
+// highest bit), last_is_win = the last applied record is the winner.
+__host__ __device__ __forceinline__ uint32_t summ_run_flags(uint32_t hes, uint32_t tms, uint32_t fl, uint32_t er,
+                                                            bool stop0, uint32_t &wm, bool &last_is_win) {
+  const uint32_t upto = tms ^ (tms - 1u); // through the first stop; all ones when there is none
+  const uint32_t app = stop0 ? 0u : (hes & upto);
+  wm = app & fl;
+  last_is_win = wm > (app & ~fl); // the highest applied bit is a failure record
+  uint32_t f = app ? (F_HAS_APP | kCodeRunning) : 0u;
+  if (er) f |= F_ERR;
+  if (tms) f |= F_STOPPED;
+  if (stop0) f |= F_STOPPED | F_FIN0;
+  if (hes != app) f |= F_SKIP; // handled records after the stop
+  return f;
+}
+// codex = code of the winner's switch arm | F_HAS_WIN | F_HAS_APP, or 0 when there is no winner.
+__host__ __device__ __forceinline__ uint32_t summ_run_finish(uint32_t f, uint32_t codex, bool last_is_win) {
+  return last_is_win ? (codex | (f & ~(F_LAST_MASK | F_WIN_MASK))) : (f | (codex & ~F_LAST_MASK));
+}
+
 // Close a job (its summary must be anchored): emit (verdict, winner_idx).
 __host__ __device__ __forceinline__ void summ_resolve(Summ s, uint32_t &verdict, uint32_t &winner) {
   verdict = (s.f & 0xFFFFu) | (s.f & F_ERR) >> 3; // a missing checkpoint also deletes the job (:268)

@@ -14,13 +14,17 @@
 //                   owner among them (they take the tiles in turn) publishes the tile's
 //                   JOB COUNT, polls predecessor tiles (decoupled look-back on counts
 //                   only) for the index of the tile's first job row and releases the workers
-//   worker warps    each warp owns a contiguous range of the tile and walks it 32
-//                   records at a time, lane per record: table lookups -> packed
-//                   verdict -> global; warp ballots -> bit masks in registers; the
-//                   lane holding the last record of a job folds the job's masks
-//                   (codes of other lanes by shuffle, the job left open by the
-//                   previous 32 records carried in registers) and stores the
-//                   16-byte job row at its final position
+//   worker warps    each warp owns a contiguous range of the tile and makes two passes
+//                   over it.  Record pass, 32 records at a time, lane per record:
+//                   table lookups -> packed verdict -> global; five warp ballots
+//                   -> one row of bit masks per 32 records, kept in the stage in
+//                   place of the columns just consumed, as are the switch arm of
+//                   every record and the list of the positions where jobs end.
+//                   Job pass, lane per JOB: a lane cuts its job's bits out of the
+//                   mask rows with funnel shifts, folds them with a dozen bit
+//                   operations and stores the 16-byte job row at its final
+//                   position — every lane does useful work, whatever the share of
+//                   records that end a job
 //   summary warp    after the workers: frees the stage, publishes the summary of
 //                   the job left open at the tile's end, and writes the few rows
 //                   the workers could not close — jobs that began before a
@@ -76,7 +80,7 @@ constexpr uint64_t kWatchdogNs = 8000000000ull; // a stuck wait traps instead of
 #endif
 constexpr int kStageBudgetBytes = NXS_SMEM_BUDGET_KB * 1024;
 template <int TILE> struct StagesFor {
-  static constexpr int per_stage = TILE * 13 + TILE / 8 + 256 + 48 * NXS_WORKERS; // ~ sizeof(StageBuf<TILE>)
+  static constexpr int per_stage = TILE * 13 + TILE / 4 + 256 + 48 * NXS_WORKERS; // ~ sizeof(StageBuf<TILE>)
   static constexpr int fit = kStageBudgetBytes / per_stage;
   static constexpr int value = fit < 2 ? 2 : fit > NXS_MAX_STAGES ? NXS_MAX_STAGES : fit;
 };
@@ -95,11 +99,17 @@ template <int TILE> struct __align__(128) StageBuf {
   // keyx[1] = key of the record before the tile, keyx[2..TILE+1] = the tile's
   // keys (16-byte aligned for the bulk copy), keyx[TILE+2] = key after the tile
   uint64_t keyx[TILE + 4];
+  // The four small columns are consumed by the record pass of a worker range and then reused IN PLACE,
+  // range by range, for what the job pass reads (a range = RANGE records of one worker warp):
+  //   reason[r0 + q]            <- u16: position + 1 (range-local) of the q-th record that ends a job
+  //   kind[r0 + i]              <- u8: 4 * switch arm of record i
+  //   flags[r0 + 16 c .. +15]   <- MaskRow of 32-record chunk c of the range (he, tm, fl, er ballots)
+  // (every write lands on bytes of records the pass has already read: q <= i, 16 c <= 32 c; stage stays)
   uint16_t reason[TILE];
   uint8_t kind[TILE];
-  uint8_t flags[TILE];
-  uint8_t stage[TILE];
-  uint32_t tailmask[TILE / 32]; // bit b: record 32*chunk + b is the last of its job
+  alignas(16) uint8_t flags[TILE];
+  alignas(16) uint8_t stage[TILE];
+  uint2 tailinfo[TILE / 32]; // .x bit b: record 32*chunk + b is the last of its job; .y: jobs ending earlier in the worker range
   RangeInfo range[kWorkerWarps];
   uint32_t range_off[kWorkerWarps]; // jobs ending before each range, tile-local
   uint32_t part_total[kCounterWarps]; // jobs ending in each counter warp's part of the tile
@@ -137,7 +147,7 @@ template <int STAGES> struct Ctl {
   // Tables of the classification pass.  Entries are pre-scaled to byte offsets so that an address is
   // one instruction: vt entry of a record = vt + lut[..] + lut2[..].
   alignas(16) uint32_t vt[64]; // [finished(stage) 0..1][gate class 0..3][arm 0..7] -> verdict | fold bits (both halves equal)
-  uint32_t code[8];            // arm -> action | new_stage << 3 | cause_tpl << 7 | msg_tpl << 9
+  uint32_t codex[8];           // arm -> action | new_stage << 3 | cause_tpl << 7 | msg_tpl << 9 | F_HAS_WIN | F_HAS_APP (0 for arm 0)
   uint8_t lut[136];            // [min(kind,3)][min(reason,32)] (row stride 33) -> 4 * switch arm (1..7, 0 = `default`)
   alignas(8) uint8_t lut2[2048]; // stage * 8 + (flags & 7) -> 32 * gate class (0 dropped, 1 no checkpoint, 2 finished,
                                  //                            3 apply) + 128 * IsFinished(stage & 15)
@@ -195,7 +205,7 @@ struct ClassifyParams {
 };
 
 template <int TILE> constexpr size_t classify_smem_bytes() {
-  return sizeof(StageBuf<TILE>) * StagesFor<TILE>::value + sizeof(Ctl<StagesFor<TILE>::value>);
+  return sizeof(StageBuf<TILE>) * StagesFor<TILE>::value; // dynamic part: the ring (Ctl is a static __shared__ object)
 }
 
 #if defined(__CUDACC__)
@@ -373,7 +383,7 @@ __device__ __forceinline__ void count_part(const ClassifyParams &p, StageBuf<TIL
         bool tail = sb.keyx[2 + i] != sb.keyx[3 + i];
         if (last_tile && i == TILE - 1) tail = true;
         const uint32_t T = __ballot_sync(0xffffffffu, tail);
-        if (lane == 0) sb.tailmask[r * CPW + j] = T;
+        if (lane == 0) sb.tailinfo[r * CPW + j] = make_uint2(T, jobs);
         jobs += __popc(T);
       }
       if (lane == 0) sb.range_off[r] = total;
@@ -381,6 +391,7 @@ __device__ __forceinline__ void count_part(const ClassifyParams &p, StageBuf<TIL
     }
     if (part == 0 && lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(sb.keyx[2] != sb.keyx[1]);
   } else { // ragged last tile (once per launch)
+    uint32_t range_start = 0; // `total` at the first chunk of the current worker range
     for (uint32_t c = part * RPP * CPW; c < (part + 1) * RPP * CPW; ++c) {
       const uint32_t i = c * 32 + lane;
       bool tail = false;
@@ -394,9 +405,10 @@ __device__ __forceinline__ void count_part(const ClassifyParams &p, StageBuf<TIL
         sb.stage[i] = p.stage[start + i];
       }
       const uint32_t T = __ballot_sync(0xffffffffu, tail);
+      if (c % CPW == 0) range_start = total;
       if (lane == 0) {
         if (c % CPW == 0) sb.range_off[c / CPW] = total;
-        sb.tailmask[c] = T;
+        sb.tailinfo[c] = make_uint2(T, total - range_start);
       }
       total += __popc(T);
     }
@@ -545,10 +557,106 @@ __device__ __forceinline__ void counter_loop(const ClassifyParams &p, StageBuf<T
 }
 
 // ---------------------------------------------------------------------- workers
+struct __align__(16) MaskRow { // ballots of one 32-record chunk (bit b = record b of the chunk)
+  uint32_t he; // handled by a switch arm, guards passed, checkpoint exists
+  uint32_t tm; // ... and the arm's new stage is a finished one (a stop)
+  uint32_t fl; // ... and the arm is a failure action
+  uint32_t er; // handled, guards passed, no checkpoint (:265-273)
+};
+#ifndef NXS_RECORD_GROUP
+#define NXS_RECORD_GROUP 4 /* 32-record steps whose loads are issued together */
+#endif
+constexpr uint32_t kRecordGroup = NXS_RECORD_GROUP;
+
+__device__ __forceinline__ uint32_t shr_clamp(uint32_t v, uint32_t n) { // n >= 32 gives 0
+  uint32_t r;
+  asm("shr.u32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(n));
+  return r;
+}
+
+// A run of more than 32 records (a long job): word by word through the mask rows.  Rare, kept out of line.
+template <int TILE, int STAGES>
+__device__ __noinline__ Summ long_run(const StageBuf<TILE> &sb, const Ctl<STAGES> &ctl, uint32_t r0, uint32_t s,
+                                      uint32_t e1, bool stop0, uint32_t gbase) {
+  const uint8_t *const arms = sb.kind + r0;
+  const MaskRow *const rows_m = reinterpret_cast<const MaskRow *>(sb.flags + r0);
+  Summ S = summ_identity();
+  for (uint32_t pos = s; pos < e1;) {
+    const uint32_t ww = pos >> 5, ss = pos & 31u;
+    const uint32_t take = min(32u - ss, e1 - pos);
+    const uint32_t m = shr_clamp(0xFFFFFFFFu, 32u - take);
+    const MaskRow r = rows_m[ww];
+    uint32_t wm;
+    bool liw;
+    const uint32_t f = summ_run_flags((r.he >> ss) & m, (r.tm >> ss) & m, r.fl >> ss, (r.er >> ss) & m, pos == s && stop0, wm, liw);
+    uint32_t codex = 0, wpos = pos;
+    if (wm) {
+      wpos = pos + hi_bit(wm);
+      codex = ctl.codex[arms[wpos] >> 2];
+    }
+    S = summ_combine(S, Summ{gbase + wpos, summ_run_finish(f, codex, liw)});
+    pos += take;
+  }
+  return S;
+}
+
+// One round of the job pass: lane `lane` takes run k = kb + lane of the range.  Run k = records
+// [ends[k-1], ends[k]) (run 0 starts at the range's first record); the caller has put the end of the
+// range behind the last job end, so the last run (k == njobs, `open_end`) is the job still open there.
+// FIRST: this round holds run 0, the only one that can have begun before the range.
+template <int TILE, bool FIRST, int STAGES>
+__device__ __forceinline__ void job_round(const ClassifyParams &p, StageBuf<TILE> &sb, const Ctl<STAGES> &ctl,
+                                          uint32_t warp, uint32_t r0, uint32_t k, uint32_t njobs, bool first_is_head,
+                                          uint32_t gbase, nxs_job_row *prow) {
+  const uint16_t *const ends = sb.reason + r0;
+  const uint8_t *const arms = sb.kind + r0;
+  const MaskRow *const rows_m = reinterpret_cast<const MaskRow *>(sb.flags + r0);
+  uint32_t s = (ends - 1)[k];
+  const uint32_t e1 = ends[k];
+  if (FIRST && k == 0) s = 0;
+  const uint32_t len = e1 - s;
+  const bool anchored = !FIRST || k != 0 || first_is_head;
+  // IsFinished() of the row the job's first record found (:276): a stop before the first record
+  const bool stop0 = anchored && ((p.finished_mask >> (sb.stage[r0 + s] & 15u)) & 1u);
+  Summ S;
+  if (len <= 32u) {
+    const uint32_t w = s >> 5, sh = s & 31u;
+    const uint4 lo = *reinterpret_cast<const uint4 *>(rows_m + w), hi = *reinterpret_cast<const uint4 *>(rows_m + w + 1);
+    const uint32_t m = shr_clamp(0xFFFFFFFFu, 32u - len);
+    uint32_t wm;
+    bool liw;
+    const uint32_t f = summ_run_flags(__funnelshift_r(lo.x, hi.x, sh) & m, __funnelshift_r(lo.y, hi.y, sh) & m,
+                                      __funnelshift_r(lo.z, hi.z, sh), __funnelshift_r(lo.w, hi.w, sh) & m, stop0, wm, liw);
+    const uint32_t wpos = s + hi_bit(wm); // (s - 1 when there is no winner: a harmless load, dropped below)
+    uint32_t codex = *reinterpret_cast<const uint32_t *>(reinterpret_cast<const uint8_t *>(ctl.codex) + arms[wpos]);
+    if (!wm) codex = 0;
+    S = Summ{gbase + wpos, summ_run_finish(f, codex, liw)};
+  } else {
+    S = long_run(sb, ctl, r0, s, e1, stop0, gbase);
+  }
+  if (k == njobs) { // the job still open at the end of the range (this run exists only when there is one)
+    if (anchored) S.f |= F_ANCHORED;
+    sb.range[warp].suffix = summ_pack(S);
+    sb.range[warp].flags = first_is_head ? RANGE_FIRST_IS_HEAD : 0u;
+    if (njobs == 0 || first_is_head) sb.range[warp].has_unres = 0;
+  } else {
+    const uint64_t key = sb.keyx[2 + r0 + e1 - 1];
+    if (anchored) {
+      uint32_t verdict, winner;
+      summ_resolve(S, verdict, winner);
+      __stcs(reinterpret_cast<uint4 *>(prow), make_uint4((uint32_t)key, (uint32_t)(key >> 32), verdict, winner));
+    } else { // the range's first job began before it: left to the summary warp
+      sb.range[warp].unres = summ_pack(S);
+      sb.range[warp].unres_key = key;
+      sb.range[warp].has_unres = 1;
+    }
+  }
+}
+
 template <int TILE, bool FULL, int STAGES>
 __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf<TILE> &sb, const Ctl<STAGES> &ctl,
                                                uint32_t tile, uint32_t warp, uint32_t lane) {
-  static_assert(TILE % (kWorkerWarps * 32) == 0, "a tile is split evenly into 32-record steps per worker warp");
+  static_assert(TILE % (kWorkerWarps * 32 * kRecordGroup) == 0, "a range is a whole number of record groups");
   constexpr uint32_t RANGE = TILE / kWorkerWarps; // records per warp
   constexpr uint32_t CPW = RANGE / 32;            // 32-record chunks per warp
   const uint32_t start = tile * TILE;
@@ -558,98 +666,78 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
     if (lane == 0) sb.range[warp] = RangeInfo{summ_pack(summ_identity()), 0ull, 0ull, 0u, 0u};
     return;
   }
-  const uint32_t le = (2u << lane) - 1u, lt = le >> 1, lanebit = 1u << lane;
-  const uint32_t row0 = sb.tile_base + sb.range_off[warp]; // index of the range's first job row
+  const uint32_t cnt_r = FULL ? RANGE : min(RANGE, cnt - r0); // records of the range that exist
+  const uint32_t lt = (1u << lane) - 1u;
   // Does the first record of the range begin a job?  (warp-uniform)
-  uint32_t prev_bit = r0 == 0 ? sb.first_is_head : sb.tailmask[r0 / 32 - 1] >> 31;
-  const uint32_t first_is_head = prev_bit;
-  Summ ctx = summ_identity(); // the job left open by the records of this range seen so far
-  uint32_t wcount = 0, closed = 0;
-  if (lane == 0) sb.range[warp].has_unres = 0;
-  __syncwarp();
+  const bool first_is_head = (r0 == 0 ? sb.first_is_head : sb.tailinfo[r0 / 32 - 1].x >> 31) != 0;
 
-  // running pointers (bumped once per step: no index arithmetic inside the loop)
-  const uint32_t i0 = r0 + lane;
-  const uint8_t *pk = sb.kind + i0, *pf = sb.flags + i0, *ps = sb.stage + i0;
-  const uint16_t *pr = sb.reason + i0;
-  const uint64_t *pkey = sb.keyx + 2 + i0;
-  const uint32_t *pt = sb.tailmask + r0 / 32;
-  uint32_t *pv = p.verdict + (start + i0);
-  uint32_t gidx = p.record_base + start + r0; // batch index of the step's first record
-  const uint32_t lut_a = smem_u32_pinned(ctl.lut), lut2_a = smem_u32_pinned(ctl.lut2);
-  const uint32_t vt_a = smem_u32_pinned(ctl.vt), code_a = smem_u32_pinned(ctl.code);
+  // What the job pass reads, written in place of the consumed columns (see StageBuf).
+  uint16_t *const ends = sb.reason + r0;
+  uint8_t *const arms = sb.kind + r0;
+  MaskRow *const rows_m = reinterpret_cast<MaskRow *>(sb.flags + r0);
 
-#pragma unroll kClassifyUnroll
-  for (uint32_t j = 0; j < CPW; ++j, pk += 32, pf += 32, ps += 32, pr += 32, pkey += 32, pt += 1, pv += 32, gidx += 32) {
-    const bool valid = FULL || i0 + j * 32 < cnt;
-    const uint32_t T = *pt;
-    uint32_t fin_self = 0, vt = 0, code = 0;
-    uint64_t key = 0;
-    if (valid) {
-      const uint32_t kind = *pk, reason = *pr, fl = *pf, st = *ps;
-      key = *pkey;
-      // onEvent: guards (:155,:161,:218) and the (kind, reason) switch arms, then superviseAction's
-      // order: no checkpoint (:265) -> finished (:276) -> switch (:283).  All of it is table lookups.
-      const uint32_t arm4 = lds_u8(lut_a + umin32(kind, 3u) * 33u + umin32(reason, 32u));
-      code = lds_u32(code_a + arm4);
-      const uint32_t l2 = lds_u8(st * 8u + ((fl & 7u) | lut2_a)); // lut2 is 8-byte aligned: | is +
-      vt = lds_u32(vt_a + arm4 + l2);
-      fin_self = (l2 << 10) & F_FIN0; // IsFinished() of the row this record saw (bit 7 of l2 -> bit 17)
-      __stcs(pv, vt & kVerdictMask);
-    }
-    const uint32_t H = T << 1 | prev_bit; // bit b: record b of the chunk begins a job
-    prev_bit = T >> 31;
-    const uint32_t HE = ballot_bit(vt, VT_HE), TM = ballot_bit(vt, VT_TERM);
-    const uint32_t FL = ballot_bit(vt, VT_FAIL), ER = ballot_bit(vt, VT_ERR);
-
-    // fold of the records from the job's first record in this chunk (or the chunk start) up to this lane
-    const uint32_t h_in = H & le;
-    const uint32_t hb = hi_bit(h_in | 1u); // h_in == 0 -> 0: the run starts at the chunk start
-    const uint32_t seg = le & (~0u << hb);
-    const uint32_t hes = HE & seg, tms = TM & seg;
-    const uint32_t upto = tms ^ (tms - 1u); // through the first stop; all ones when there is none
-    const uint32_t app = hes & upto;        // applied records (under the premise)
-    const uint32_t wm = app & FL;           // ... with a failure action
-    const uint32_t wp = hi_bit(wm | 1u);    // the winner: the last of them
-    const uint32_t code_w = __shfl_sync(0xffffffffu, code, wp);
-    const uint32_t fin_head = __shfl_sync(0xffffffffu, fin_self, hb);
-    // summary flags: a non-failure handled record is a ToRunning; the winner brings cause / message, and
-    // action / stage too when nothing was applied after it
-    const uint32_t winbits = (code_w & (F_WIN_MASK | F_LAST_MASK)) | F_HAS_WIN | F_HAS_APP;
-    uint32_t f = hes ? (F_HAS_APP | kCodeRunning) : 0u;
-    if (wm) f = ((app >> wp) == 1u) ? winbits : (f | (winbits & ~F_LAST_MASK));
-    if (ER & seg) f |= F_ERR;
-    if (tms) f |= F_STOPPED;
-    if (hes & ~upto) f |= F_SKIP;
-    Summ S{gidx + wp, f};
-    if (h_in) S.f = summ_anchor_flags(S.f, fin_head); // the job begins in this chunk
-    else S = summ_combine(ctx, S);          // it continues the job left open before the chunk
-
-    if (T & lanebit) { // this record ends a job: close it and store its row
-      if (S.f & F_ANCHORED) {
-        uint32_t verdict, winner;
-        summ_resolve(S, verdict, winner);
-        __stcs(reinterpret_cast<uint4 *>(p.rows + (row0 + wcount + __popc(T & lt))),
-               make_uint4((uint32_t)key, (uint32_t)(key >> 32), verdict, winner));
-      } else { // only the first job of a range can have begun before it: left to the summary warp
-        sb.range[warp].unres = summ_pack(S);
-        sb.range[warp].unres_key = key;
-        sb.range[warp].has_unres = 1;
+  // ------------------------------------------------------------------ record pass
+  // onEvent: guards (:155,:161,:218) and the (kind, reason) switch arms, then superviseAction's order:
+  // no checkpoint (:265) -> finished (:276) -> switch (:283).  All of it is table lookups.
+  uint32_t njobs = 0, last_T = 0;
+  uint32_t *pv = p.verdict + (size_t)start + r0 + lane;
+#pragma unroll 1
+  for (uint32_t g = 0; g < CPW; g += kRecordGroup, pv += 32 * kRecordGroup) {
+    uint2 ti[kRecordGroup];
+    uint32_t vt[kRecordGroup], arm4[kRecordGroup];
+    // loads and lookups of the whole group first: the stores below land on bytes read here
+#pragma unroll
+    for (uint32_t u = 0; u < kRecordGroup; ++u) {
+      const uint32_t i = (g + u) * 32 + lane;
+      ti[u] = sb.tailinfo[r0 / 32 + g + u];
+      vt[u] = 0;
+      arm4[u] = 0;
+      if (FULL || i < cnt_r) {
+        const uint32_t kind = sb.kind[r0 + i], reason = sb.reason[r0 + i], fl = sb.flags[r0 + i], st = sb.stage[r0 + i];
+        arm4[u] = ctl.lut[umin32(kind, 3u) * 33u + umin32(reason, 32u)];
+        const uint32_t l2 = ctl.lut2[st * 8u + (fl & 7u)];
+        vt[u] = *reinterpret_cast<const uint32_t *>(reinterpret_cast<const uint8_t *>(ctl.vt) + (arm4[u] + l2));
+        __stcs(pv + 32 * u, vt[u] & kVerdictMask);
       }
     }
-    wcount += __popc(T);
-    if (FULL || r0 + j * 32 + 31 < cnt) closed = T >> 31; // (FULL: compile time)
-    else closed = 1; // the ragged (hence last) tile ends inside this chunk: its last record closes a job
-    ctx = shfl_summ(S, 31);
-#ifdef NXS_TRACE_STEPS
-    if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_STEP, tile | j << 24);
-#endif
+#pragma unroll
+    for (uint32_t u = 0; u < kRecordGroup; ++u) {
+      const uint32_t c = g + u, i = c * 32 + lane;
+      const uint32_t HE = ballot_bit(vt[u], VT_HE), TM = ballot_bit(vt[u], VT_TERM);
+      const uint32_t FL = ballot_bit(vt[u], VT_FAIL), ER = ballot_bit(vt[u], VT_ERR);
+      if (FULL || i < cnt_r) arms[i] = (uint8_t)arm4[u];
+      if (lane == 0) *reinterpret_cast<uint4 *>(rows_m + c) = make_uint4(HE, TM, FL, ER);
+      const uint32_t T = ti[u].x;
+      if ((T >> lane) & 1u) ends[ti[u].y + __popc(T & lt)] = (uint16_t)(i + 1);
+      if (u == kRecordGroup - 1) njobs = ti[u].y + __popc(T), last_T = T;
+    }
+  }
+  // Does the range end on a job boundary?  If not, the end of the range closes the list: the run behind
+  // the last job end is the job still open there.  (Then njobs < RANGE, so the entry exists.)
+  const bool closed = FULL ? (last_T >> 31) != 0 : (sb.tailinfo[(r0 + cnt_r - 1) / 32].x >> ((cnt_r - 1) & 31u)) & 1u;
+  if (lane == 0) {
+    if (!closed) ends[njobs] = (uint16_t)cnt_r;
+    else { // nothing flows out of the range
+      sb.range[warp].suffix = summ_pack(Summ{0u, F_ANCHORED});
+      sb.range[warp].flags = RANGE_CLOSED | (first_is_head ? RANGE_FIRST_IS_HEAD : 0u);
+      if (njobs == 0 || first_is_head) sb.range[warp].has_unres = 0;
+    }
   }
   __syncwarp();
-  if (lane == 0) {
-    sb.range[warp].suffix = summ_pack(ctx);
-    sb.range[warp].flags = (closed ? RANGE_CLOSED : 0u) | (first_is_head ? RANGE_FIRST_IS_HEAD : 0u);
+
+  // --------------------------------------------------------------------- job pass (a lane per run)
+  const uint32_t nruns = njobs + (closed ? 0u : 1u);
+  const uint32_t gbase = p.record_base + start + r0; // batch index of the range's first record
+  nxs_job_row *prow = p.rows + ((size_t)sb.tile_base + sb.range_off[warp] + lane); // row of run `lane`
+  if (lane < nruns) job_round<TILE, true, STAGES>(p, sb, ctl, warp, r0, lane, njobs, first_is_head, gbase, prow);
+#pragma unroll 1
+  for (uint32_t k = 32 + lane; k < nruns; k += 32) {
+    prow += 32;
+    job_round<TILE, false, STAGES>(p, sb, ctl, warp, r0, k, njobs, first_is_head, gbase, prow);
   }
+  // the stage's columns were written here through the generic proxy; the next tile lands in them through the async proxy
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncwarp();
 }
 
 template <int TILE, int STAGES>
@@ -887,7 +975,8 @@ __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__
   // address space, so accesses compile to LDS/STS rather than generic loads)
   extern __shared__ __align__(128) uint8_t smem_raw[];
   StageBuf<TILE> *stages = reinterpret_cast<StageBuf<TILE> *>(smem_raw);
-  Ctl<STAGES> &ctl = *reinterpret_cast<Ctl<STAGES> *>(smem_raw + sizeof(StageBuf<TILE>) * STAGES);
+  // static, so that the addresses of the barriers and tables are immediates in the hot loops
+  __shared__ Ctl<STAGES> ctl;
   const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   if (tid == 0) {
@@ -907,7 +996,7 @@ __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__
     const uint32_t fin = (p.finished_mask >> st) & 1u;
     ctl.lut2[e] = (uint8_t)(32u * ((fl & 3u) != 3u ? 0u : !(fl & NXS_FLAG_CHECKPOINT) ? 1u : fin ? 2u : 3u) + 128u * fin);
   }
-  if (tid < 8) ctl.code[tid] = p.code[tid];
+  if (tid < 8) ctl.codex[tid] = p.code[tid] ? (p.code[tid] | F_HAS_WIN | F_HAS_APP) : 0u;
   if (tid >= 128 && tid < 192) {
     const uint32_t e = tid - 128, g = (e >> 3) & 3u, arm = e & 7u;
     const uint32_t code = p.code[arm], a = code & 7u, msg = code >> 9;

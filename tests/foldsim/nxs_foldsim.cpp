@@ -11,6 +11,7 @@
 // only published their aggregate so far.
 #include <cstdint>
 #include <cstring>
+#include <algorithm>
 #include <vector>
 
 #include "nxs_device.cuh"
@@ -156,5 +157,123 @@ extern "C" int nxs_foldsim(const uint8_t *kind, const uint16_t *reason, const ui
     }
     *n_jobs = desc[t].inc_count;
   }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// Walk-through of the kernel's worker pass as it is since the job pass has one lane per job: every
+// worker range of `range_records` records is processed the way classify_range / job_round do it —
+// record pass: ballot words per 32-record chunk (MaskRow) and the list of job ends; job pass: every
+// run of records [ends[k-1], ends[k]) is cut out of the mask rows (funnel shift for runs of up to 32
+// records, word by word for longer ones) and summarised with the product's summ_run_flags /
+// summ_run_finish; the run that began before the range is left open (`unres`), the one still open at
+// its end is the `suffix`.  Ranges are stitched sequentially with summ_combine (the kernel does that
+// in the summary warp and through the look-back).
+namespace {
+struct Row4 { uint32_t he, tm, fl, er; };
+inline uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh) {
+  return sh ? (lo >> sh) | (hi << (32u - sh)) : lo;
+}
+inline uint32_t shr_clamp(uint32_t v, uint32_t n) { return n >= 32u ? 0u : v >> n; }
+} // namespace
+
+extern "C" int nxs_foldsim_ranges(const uint8_t *kind, const uint16_t *reason, const uint8_t *flags,
+                                  const uint8_t *stage, const uint64_t *key, uint64_t n, uint16_t finished_mask,
+                                  uint32_t range_records, uint32_t *verdict, nxs_job_row *rows, uint64_t *n_jobs) {
+  if (range_records == 0 || range_records % 32) return -1;
+  uint8_t lut[128];
+  uint16_t code_of_arm[8];
+  nxs_build_lut(lut, code_of_arm);
+  uint32_t term_mask = 0;
+  for (uint32_t a = 1; a <= 4; ++a)
+    if ((finished_mask >> new_stage_of(a)) & 1u) term_mask |= 1u << a;
+  const uint32_t RANGE = range_records, CPW = RANGE / 32;
+  std::vector<Row4> mrow(CPW + 2);
+  std::vector<uint16_t> ends(RANGE + 1);
+  std::vector<uint8_t> arm(RANGE);
+  Summ open = summ_identity(); // the job open at the end of the previous range, from its first record on
+  uint64_t n_rows = 0;
+
+  for (uint64_t start = 0; start < n; start += RANGE) {
+    const uint32_t cnt_r = (uint32_t)((n - start) < RANGE ? (n - start) : RANGE);
+    const bool first_is_head = start == 0 || key[start] != key[start - 1];
+    // ---- record pass
+    std::fill(mrow.begin(), mrow.end(), Row4{0, 0, 0, 0});
+    uint32_t njobs = 0;
+    for (uint32_t i = 0; i < cnt_r; ++i) {
+      const uint64_t g = start + i;
+      const uint32_t fl = flags[g], st = stage[g] & 15u;
+      const uint32_t k = kind[g] < 3 ? kind[g] : 3u;
+      const uint32_t am = lut[k * 32u + (reason[g] < 32u ? reason[g] : 0u)];
+      const uint32_t cd = ((fl & 3u) == 3u) ? code_of_arm[am] : 0u;
+      const uint32_t a = cd & 7u;
+      const bool exists = (fl & NXS_FLAG_CHECKPOINT) != 0;
+      const bool finished = (finished_mask >> st) & 1u;
+      const uint32_t base = exists ? (finished ? (a | 1u << 14) : (a ? applied_verdict(a) : 0u))
+                                   : (a | 1u << 12 | NXS_ERR_NO_CHECKPOINT << 15);
+      verdict[g] = a ? (base | (cd >> 9) << 9) : 0u;
+      arm[i] = (uint8_t)am;
+      const bool he = a != 0 && exists;
+      Row4 &m = mrow[i >> 5];
+      const uint32_t bit = 1u << (i & 31);
+      if (he) m.he |= bit;
+      if (he && ((term_mask >> a) & 1u)) m.tm |= bit;
+      if (he && a != NXS_ACTION_RUNNING) m.fl |= bit;
+      if (a != 0 && !exists) m.er |= bit;
+      if (g + 1 == n || key[g] != key[g + 1]) ends[njobs++] = (uint16_t)(i + 1);
+    }
+    const bool closed = njobs > 0 && ends[njobs - 1] == cnt_r;
+    if (!closed) ends[njobs] = (uint16_t)cnt_r;
+    const uint32_t nruns = njobs + (closed ? 0u : 1u);
+    // ---- job pass
+    Summ suffix{0u, F_ANCHORED};
+    for (uint32_t k = 0; k < nruns; ++k) {
+      const uint32_t s = k ? ends[k - 1] : 0u, e1 = ends[k], len = e1 - s;
+      const bool anchored = k != 0 || first_is_head;
+      const bool stop0 = anchored && ((finished_mask >> (stage[start + s] & 15u)) & 1u);
+      const uint32_t gbase = (uint32_t)start;
+      Summ S;
+      if (len <= 32u) {
+        const uint32_t w = s >> 5, sh = s & 31u, m = shr_clamp(0xFFFFFFFFu, 32u - len);
+        const Row4 lo = mrow[w], hi = mrow[w + 1];
+        uint32_t wm;
+        bool liw;
+        const uint32_t f = summ_run_flags(funnel_r(lo.he, hi.he, sh) & m, funnel_r(lo.tm, hi.tm, sh) & m,
+                                          funnel_r(lo.fl, hi.fl, sh), funnel_r(lo.er, hi.er, sh) & m, stop0, wm, liw);
+        const uint32_t wpos = wm ? s + hi_bit(wm) : s;
+        const uint32_t codex = wm ? (code_of_arm[arm[wpos]] | F_HAS_WIN | F_HAS_APP) : 0u;
+        S = Summ{gbase + wpos, summ_run_finish(f, codex, liw)};
+      } else {
+        S = summ_identity();
+        for (uint32_t pos = s; pos < e1;) {
+          const uint32_t ww = pos >> 5, ss = pos & 31u;
+          const uint32_t take = std::min(32u - ss, e1 - pos), m = shr_clamp(0xFFFFFFFFu, 32u - take);
+          const Row4 r = mrow[ww];
+          uint32_t wm;
+          bool liw;
+          const uint32_t f = summ_run_flags((r.he >> ss) & m, (r.tm >> ss) & m, r.fl >> ss, (r.er >> ss) & m,
+                                            pos == s && stop0, wm, liw);
+          uint32_t codex = 0, wpos = pos;
+          if (wm) {
+            wpos = pos + hi_bit(wm);
+            codex = code_of_arm[arm[wpos]] | F_HAS_WIN | F_HAS_APP;
+          }
+          S = summ_combine(S, Summ{gbase + wpos, summ_run_finish(f, codex, liw)});
+          pos += take;
+        }
+      }
+      if (anchored) S.f |= F_ANCHORED;
+      if (k == njobs) {
+        suffix = S;
+      } else {
+        if (!anchored) S = summ_combine(open, S); // the run began in an earlier range
+        uint32_t v, win;
+        summ_resolve(S, v, win);
+        rows[n_rows++] = nxs_job_row{key[start + e1 - 1], v, win};
+      }
+    }
+    open = (suffix.f & F_ANCHORED) ? suffix : summ_combine(open, suffix);
+  }
+  *n_jobs = n_rows;
   return 0;
 }

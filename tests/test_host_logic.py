@@ -119,3 +119,50 @@ def test_tile_algorithm_synthetic_stream():
         want = cpu_oracle.classify(cols)
         got = foldsim(cols, util.FM_DEFAULT, 2048)
         util.assert_same(*got, *want, f"workload={workload}")
+
+
+# ------------------------------------------------------------------ worker-range walk-through (lane per job)
+def foldsim_ranges(cols, fm, range_records):
+    global _sim
+    if _sim is None:
+        _sim = C.CDLL(os.path.join(ROOT, "tests", "foldsim", "_build", "libnxs_foldsim.so"))
+    n = len(cols["kind"])
+    v = np.zeros(n, np.uint32)
+    rows = np.zeros(n, cpu_oracle.JOB_ROW)
+    nj = C.c_uint64(0)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    rc = _sim.nxs_foldsim_ranges(p(cols["kind"]), p(cols["reason_id"]), p(cols["flags"]), p(cols["cur_stage"]),
+                                 p(cols["job_key"]), C.c_uint64(n), C.c_uint16(fm), C.c_uint32(range_records),
+                                 p(v), p(rows), C.byref(nj))
+    assert rc == 0
+    return v, rows[:nj.value]
+
+
+@pytest.mark.parametrize("fm", util.MASKS)
+def test_job_pass_exhaustive_domain(fm):
+    """The job pass of the kernel (one lane per job: runs cut out of the ballot words by funnel shifts,
+    summ_run_flags / summ_run_finish) over every (kind, reason, flags, stage) combination."""
+    for per_job in (1, 2, 5, 33):
+        cols = util.exhaustive_cols(per_job)
+        util.assert_same(*foldsim_ranges(cols, fm, 128), *cpu_oracle.classify(cols, fm), f"per_job={per_job}")
+
+
+@pytest.mark.parametrize("range_records", [32, 128, 256, 512])
+def test_job_pass_random_jobs_cross_ranges(range_records):
+    """Runs of 1..3000 records: inside a 32-record word, straddling words (funnel shift), longer than 32
+    records (word by word) and straddling worker ranges (unres / suffix stitched with summ_combine)."""
+    rng = np.random.default_rng(range_records)
+    for trial in range(60):
+        n = int(rng.integers(1, 9000))
+        max_len = int(rng.choice([1, 2, 3, 8, 31, 32, 33, 40, 200, 3000]))
+        cols = util.random_cols(rng, n, max_len, wide=bool(trial % 3))
+        fm = int(rng.choice(util.MASKS + [int(rng.integers(0, 65536))]))
+        want = cpu_oracle.classify(cols, fm)
+        util.assert_same(*foldsim_ranges(cols, fm, range_records), *want,
+                         f"trial={trial} n={n} max_len={max_len} fm={fm:#x}")
+
+
+def test_job_pass_synthetic_stream():
+    for workload in (1, 2):
+        cols = cpu_oracle.generate(workload, 200_000)
+        util.assert_same(*foldsim_ranges(cols, util.FM_DEFAULT, 512), *cpu_oracle.classify(cols), f"workload={workload}")
