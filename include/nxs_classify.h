@@ -108,6 +108,11 @@ enum {
 
 /* ---------------------------------------------------------------- verdict
  * One u32 per record and one per job row.
+ * The PER-RECORD verdict is what the record would get on its own against the checkpoint stage
+ * in its own cur_stage: it ignores the earlier records of the same job, so records that follow
+ * a stop of their job still carry upsert / delete_job.  It is diagnostic.  I/O (Jobs().Delete,
+ * UpsertCheckpoint) must be driven from the JOB ROWS only: they hold the outcome of the
+ * reference's sequential replay with its IsFinished() guard (services/supervisor.go:276-279).
  *   bits  0-2  action        DecisionAction id
  *   bits  3-6  new_stage     stage id written by the upsert (0 unless upsert)
  *   bits  7-8  cause_tpl     nxs_cause_template index (0 = cause untouched)
@@ -175,7 +180,9 @@ typedef struct nxs_ctx nxs_ctx;
 int nxs_create(int device, uint64_t max_records, uint16_t finished_mask,
                nxs_ctx **out);
 void nxs_destroy(nxs_ctx *ctx);
-/* Use an existing cudaStream_t (passed as void*) instead of the ctx's own. */
+/* Use an existing cudaStream_t (passed as void*) instead of the ctx's own.  Work already queued
+ * by this ctx on its previous stream is waited for first (launches of one ctx share scratch).
+ * Every entry point leaves the calling thread's current CUDA device as it found it. */
 int nxs_set_stream(nxs_ctx *ctx, void *cuda_stream);
 int nxs_sync(nxs_ctx *ctx);
 const char *nxs_strerror(int status);
@@ -237,6 +244,26 @@ const char *nxs_cause_template(uint32_t idx);
 /* ------------------------------------------------------------- sharding */
 /* Shard of a job for a G-GPU run: splitmix64(job_key) % n_shards. */
 uint32_t nxs_shard_of(uint64_t job_key, uint32_t n_shards);
+
+/* One host batch on several GPUs.  The unit of dependence of the path is one job = one
+ * checkpoint row — superviseAction reads and writes only the row of its (algorithm, id)
+ * (services/supervisor.go:264,:301; primary key test-resources/checkpoints.cql:22) — so a batch
+ * can be split by job: nxs_classify_sharded partitions the records by nxs_shard_of(job_key,
+ * n_shards) without ever splitting a job, classifies every shard with its own ctx through
+ * nxs_classify (shard s runs on devices[s % n_devices]: one GPU per shard when there are
+ * enough, round-robin otherwise), and puts the results back in stream order on the host:
+ * out->verdict[i] belongs to record i, out->job_rows are ordered by the position at which
+ * each job ends in the batch and their winner_idx are batch indices — bit for bit what one
+ * nxs_classify call over the whole batch returns.  No collective and no peer access is
+ * involved: the "gather" is G independent device-to-host copies plus a host merge.
+ * Host pointers; the handle owns pinned staging buffers that grow to the largest shard seen.
+ * Not thread-safe per handle. */
+typedef struct nxs_sharded nxs_sharded;
+int nxs_sharded_create(uint32_t n_shards, const int *devices, uint32_t n_devices, uint64_t max_records,
+                       uint16_t finished_mask, nxs_sharded **out);
+void nxs_sharded_destroy(nxs_sharded *h);
+int nxs_classify_sharded(nxs_sharded *h, const nxs_batch *in, const nxs_out *out);
+const char *nxs_sharded_last_error(const nxs_sharded *h);
 
 /* ------------------------------------------------- synthetic workloads */
 enum { NXS_WORKLOAD_UNIFORM = 1, NXS_WORKLOAD_SKEWED = 2 };

@@ -59,6 +59,11 @@ SIGNATURES = {
     "nxs_msg_template": (C.c_char_p, [C.c_uint32]),
     "nxs_cause_template": (C.c_char_p, [C.c_uint32]),
     "nxs_shard_of": (C.c_uint32, [C.c_uint64, C.c_uint32]),
+    "nxs_sharded_create": (C.c_int, [C.c_uint32, C.POINTER(C.c_int), C.c_uint32, C.c_uint64, C.c_uint16,
+                                     C.POINTER(C.c_void_p)]),
+    "nxs_sharded_destroy": (None, [C.c_void_p]),
+    "nxs_classify_sharded": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(Out)]),
+    "nxs_sharded_last_error": (C.c_char_p, [C.c_void_p]),
     "nxs_generate_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32,
                                       C.c_uint32, C.POINTER(Columns), u64p]),
 }

@@ -157,3 +157,56 @@ class Classifier:
         self._check(self._lib.nxs_generate_device(self._ctx, workload, seed, first, n, shard, n_shards,
                                                   C.byref(cols), C.byref(kept)))
         return int(kept.value)
+
+
+class ShardedClassifier:
+    """One host batch on several GPUs (nxs_classify_sharded): records are partitioned by
+    splitmix64(job_key) % n_shards without splitting a job, each shard is classified by its own
+    ctx (shard s on devices[s % len(devices)]) and the results come back in stream order."""
+
+    def __init__(self, n_shards, devices=None, max_records=1 << 20, finished_mask=FINISHED_MASK_DEFAULT):
+        self._lib = _abi.load()
+        self._h = C.c_void_p()
+        if devices is None:
+            devices = [0]
+        arr = (C.c_int * len(devices))(*devices)
+        rc = self._lib.nxs_sharded_create(n_shards, arr, len(devices), max_records, finished_mask, C.byref(self._h))
+        if rc != _abi.NXS_OK:
+            self._h = None
+            raise NxsError(rc, f"nxs_sharded_create(n_shards={n_shards}, devices={list(devices)})")
+        self.n_shards = n_shards
+        self.devices = list(devices)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.nxs_sharded_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def classify(self, cols, out_verdict=None, out_rows=None):
+        """Same contract as Classifier.classify: (verdict u32[n], rows JOB_ROW[n_jobs]) in stream order."""
+        kind = np.ascontiguousarray(cols["kind"], dtype=np.uint8)
+        reason = np.ascontiguousarray(cols["reason_id"], dtype=np.uint16)
+        flags = np.ascontiguousarray(cols["flags"], dtype=np.uint8)
+        stage = np.ascontiguousarray(cols["cur_stage"], dtype=np.uint8)
+        key = np.ascontiguousarray(cols["job_key"], dtype=np.uint64)
+        n = len(kind)
+        if not (len(reason) == len(flags) == len(stage) == len(key) == n):
+            raise ValueError("columns differ in length")
+        verdict = out_verdict if out_verdict is not None else np.empty(n, dtype=np.uint32)
+        rows = out_rows if out_rows is not None else np.empty(n, dtype=JOB_ROW)
+        n_jobs = C.c_uint64(0)
+        batch = _abi.Batch(kind.ctypes.data, reason.ctypes.data, flags.ctypes.data, stage.ctypes.data,
+                           key.ctypes.data, n)
+        out = _abi.Out(verdict.ctypes.data, rows.ctypes.data, C.addressof(n_jobs))
+        rc = self._lib.nxs_classify_sharded(self._h, C.byref(batch), C.byref(out))
+        if rc != _abi.NXS_OK:
+            raise NxsError(rc, self._lib.nxs_sharded_last_error(self._h).decode())
+        return verdict[:n], rows[:n_jobs.value]

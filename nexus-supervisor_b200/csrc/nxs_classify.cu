@@ -57,6 +57,22 @@ int fail_cuda(nxs_ctx *ctx, cudaError_t e, const char *what) {
     if (e_ != cudaSuccess) return fail_cuda(ctx, e_, #call); \
   } while (0)
 
+// Makes `device` current for the calling thread and puts the caller's device back on scope exit: a
+// multi-GPU host (torch, a per-GPU worker pool) must not find its current device changed by a call.
+struct DeviceGuard {
+  int prev = -1;
+  cudaError_t status;
+  explicit DeviceGuard(int device) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    status = cudaSetDevice(device);
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+  DeviceGuard(const DeviceGuard &) = delete;
+  DeviceGuard &operator=(const DeviceGuard &) = delete;
+};
+
 int fail_arg(nxs_ctx *ctx, const char *msg) {
   if (ctx) snprintf(ctx->err, sizeof ctx->err, "%s", msg);
   return NXS_ERR_ARG;
@@ -138,7 +154,8 @@ int nxs_create(int device, uint64_t max_records, uint16_t finished_mask, nxs_ctx
     nxs_destroy(ctx);
     return code;
   };
-  if (cudaSetDevice(device) != cudaSuccess) return bail(NXS_ERR_CUDA);
+  DeviceGuard guard(device);
+  if (guard.status != cudaSuccess) return bail(NXS_ERR_CUDA);
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return bail(NXS_ERR_CUDA);
   if (prop.major < 10) return bail(NXS_ERR_NO_DEVICE); // sm_100a code only
@@ -171,7 +188,7 @@ int nxs_create(int device, uint64_t max_records, uint16_t finished_mask, nxs_ctx
 
 void nxs_destroy(nxs_ctx *ctx) {
   if (!ctx) return;
-  cudaSetDevice(ctx->device);
+  DeviceGuard guard(ctx->device);
   if (ctx->stream && ctx->own_stream) {
     cudaStreamSynchronize(ctx->stream);
     cudaStreamDestroy(ctx->stream);
@@ -197,10 +214,11 @@ void nxs_destroy(nxs_ctx *ctx) {
 
 int nxs_set_stream(nxs_ctx *ctx, void *cuda_stream) {
   if (!ctx) return NXS_ERR_ARG;
-  if (ctx->own_stream && ctx->stream) {
-    cudaStreamSynchronize(ctx->stream);
-    cudaStreamDestroy(ctx->stream);
-  }
+  DeviceGuard guard(ctx->device);
+  // Launches of one ctx share its tile descriptors and counters: whatever the old stream still holds
+  // must be done before work can be queued on another stream.
+  if (ctx->launches > 0 || ctx->own_stream) NXS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
   ctx->stream = static_cast<cudaStream_t>(cuda_stream);
   ctx->own_stream = false;
   return NXS_OK;
@@ -208,6 +226,7 @@ int nxs_set_stream(nxs_ctx *ctx, void *cuda_stream) {
 
 int nxs_sync(nxs_ctx *ctx) {
   if (!ctx) return NXS_ERR_ARG;
+  DeviceGuard guard(ctx->device);
   NXS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return NXS_OK;
 }
@@ -230,7 +249,8 @@ static int launch_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out
              (unsigned long long)ctx->max_records);
     return NXS_ERR_CAPACITY;
   }
-  NXS_CUDA(ctx, cudaSetDevice(ctx->device));
+  DeviceGuard guard(ctx->device);
+  NXS_CUDA(ctx, guard.status);
   if (in->n == 0) {
     NXS_CUDA(ctx, cudaMemsetAsync(out->n_jobs, 0, sizeof(uint64_t), ctx->stream));
     return NXS_OK;
@@ -323,36 +343,14 @@ static int ensure_staging(nxs_ctx *ctx, uint64_t slice) {
 // (copy stream 1) while slice k is classified (ctx stream) and slice k-1 is downloaded (copy stream
 // 2), with two device buffer sets.  Job rows of consecutive slices are appended in the caller's
 // buffer, so a slice's rows are downloaded once the job count of the previous one is known.
-int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
-  if (!ctx || !in || !out) return NXS_ERR_ARG;
-  if (!out->n_jobs) return fail_arg(ctx, "out->n_jobs is null");
-  if (in->n > ctx->max_records) return NXS_ERR_CAPACITY;
-  if (in->n == 0) {
-    *out->n_jobs = 0;
-    return NXS_OK;
-  }
-  if (!in->kind || !in->reason_id || !in->flags || !in->cur_stage || !in->job_key || !out->verdict ||
-      !out->job_rows)
-    return fail_arg(ctx, "null column pointer");
-  NXS_CUDA(ctx, cudaSetDevice(ctx->device));
+static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out, uint64_t slice_cap) {
   const uint64_t n = in->n;
-  // A slice may grow past kHostSliceRecords to reach the end of its last job; leave room for that.
-  const uint64_t slice_cap = n <= kHostSliceRecords ? n : kHostSliceRecords + (kHostSliceRecords >> 3);
-  int rc = ensure_staging(ctx, slice_cap);
-  if (rc != NXS_OK) {
-    cudaGetLastError();
-    snprintf(ctx->err, sizeof ctx->err, "cannot set up device staging for slices of %llu records",
-             (unsigned long long)slice_cap);
-    return rc;
-  }
   const uint64_t cap = ctx->staged_records;
   cudaStream_t s_comp = ctx->stream;
-  // everything enqueued earlier on the ctx stream must be done before the copy streams touch the staging
-  NXS_CUDA(ctx, cudaStreamSynchronize(s_comp));
-
   uint64_t lo = 0, rows_done = 0;
   uint64_t pend_lo[2] = {0, 0}, pend_n[2] = {0, 0}; // slices whose rows are still to be downloaded
   bool pending[2] = {false, false};
+  int rc = NXS_OK;
   auto finish_slice = [&](int b) -> int { // job count is (about to be) on the host: download the rows
     NXS_CUDA(ctx, cudaEventSynchronize(ctx->e_count[b]));
     const uint64_t jobs = ctx->h_njobs[b];
@@ -361,8 +359,9 @@ int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
                (unsigned long long)jobs, (unsigned long long)pend_n[b]);
       return NXS_ERR_CUDA;
     }
-    NXS_CUDA(ctx, cudaMemcpyAsync(out->job_rows + rows_done, ctx->d_rows[b], jobs * sizeof(nxs_job_row),
-                                  cudaMemcpyDeviceToHost, ctx->s_d2h));
+    if (out->job_rows)
+      NXS_CUDA(ctx, cudaMemcpyAsync(out->job_rows + rows_done, ctx->d_rows[b], jobs * sizeof(nxs_job_row),
+                                    cudaMemcpyDeviceToHost, ctx->s_d2h));
     NXS_CUDA(ctx, cudaEventRecord(ctx->e_d2h[b], ctx->s_d2h));
     rows_done += jobs;
     pending[b] = false;
@@ -411,7 +410,8 @@ int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
     NXS_CUDA(ctx, cudaStreamWaitEvent(ctx->s_d2h, ctx->e_kernel[b], 0));
     NXS_CUDA(ctx, cudaMemcpyAsync(ctx->h_njobs + b, ctx->d_njobs + b, 8, cudaMemcpyDeviceToHost, ctx->s_d2h));
     NXS_CUDA(ctx, cudaEventRecord(ctx->e_count[b], ctx->s_d2h));
-    NXS_CUDA(ctx, cudaMemcpyAsync(out->verdict + lo, ctx->d_verdict[b], m * 4, cudaMemcpyDeviceToHost, ctx->s_d2h));
+    if (out->verdict)
+      NXS_CUDA(ctx, cudaMemcpyAsync(out->verdict + lo, ctx->d_verdict[b], m * 4, cudaMemcpyDeviceToHost, ctx->s_d2h));
     pend_lo[b] = lo;
     pend_n[b] = m;
     pending[b] = true;
@@ -429,6 +429,42 @@ int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
   NXS_CUDA(ctx, cudaStreamSynchronize(s_comp));
   *out->n_jobs = rows_done;
   return NXS_OK;
+}
+
+int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
+  if (!ctx || !in || !out) return NXS_ERR_ARG;
+  if (!out->n_jobs) return fail_arg(ctx, "out->n_jobs is null");
+  if (in->n > ctx->max_records) return NXS_ERR_CAPACITY;
+  if (in->n == 0) {
+    *out->n_jobs = 0;
+    return NXS_OK;
+  }
+  if (!in->kind || !in->reason_id || !in->flags || !in->cur_stage || !in->job_key || !out->verdict ||
+      !out->job_rows)
+    return fail_arg(ctx, "null column pointer");
+  DeviceGuard guard(ctx->device);
+  NXS_CUDA(ctx, guard.status);
+  // A slice may grow past kHostSliceRecords to reach the end of its last job; leave room for that.
+  const uint64_t slice_cap = in->n <= kHostSliceRecords ? in->n : kHostSliceRecords + (kHostSliceRecords >> 3);
+  int rc = ensure_staging(ctx, slice_cap);
+  if (rc != NXS_OK) {
+    cudaGetLastError();
+    snprintf(ctx->err, sizeof ctx->err, "cannot set up device staging for slices of %llu records",
+             (unsigned long long)slice_cap);
+    return rc;
+  }
+  // everything enqueued earlier on the ctx stream must be done before the copy streams touch the staging
+  NXS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  rc = classify_slices(ctx, in, out, slice_cap);
+  if (rc != NXS_OK) {
+    // The caller owns its buffers again the moment this returns: nothing queued for an earlier slice
+    // (uploads reading the columns, downloads writing verdicts and rows) may outlive the call.
+    cudaStreamSynchronize(ctx->s_h2d);
+    cudaStreamSynchronize(ctx->stream);
+    cudaStreamSynchronize(ctx->s_d2h);
+    cudaGetLastError();
+  }
+  return rc;
 }
 
 int nxs_alloc_host(size_t bytes, void **out) {
@@ -508,7 +544,8 @@ extern "C" int nxs_classify_device_noalloc(int device, void *cuda_stream, uint16
   if (!in || !out || !out->n_jobs) return NXS_ERR_ARG;
   if (in->n > NXS_NOALLOC_MAX_RECORDS) return NXS_ERR_NOALLOC_LIMIT; // refused before anything is touched
   if (device < 0 || device >= kNoallocMaxDevices) return NXS_ERR_ARG;
-  if (cudaSetDevice(device) != cudaSuccess) {
+  DeviceGuard guard(device); // (the caller's current device is put back on return)
+  if (guard.status != cudaSuccess) {
     cudaGetLastError();
     return NXS_ERR_ARG;
   }

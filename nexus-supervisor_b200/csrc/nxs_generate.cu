@@ -179,6 +179,11 @@ extern "C" int nxs_generate_device(nxs_ctx *ctx, int workload, uint64_t seed, ui
   if (workload != NXS_WORKLOAD_UNIFORM && workload != NXS_WORKLOAD_SKEWED) return NXS_ERR_ARG;
   if (n_shards == 0) n_shards = 1;
   if (shard >= n_shards) return NXS_ERR_ARG;
+  struct Restore { // the caller's current device is put back on return
+    int prev = -1;
+    Restore() { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; }
+    ~Restore() { if (prev >= 0) cudaSetDevice(prev); }
+  } restore;
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) return fail(e, "cudaSetDevice");
   if (n == 0) {

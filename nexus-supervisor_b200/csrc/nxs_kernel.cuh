@@ -627,7 +627,7 @@ __device__ __forceinline__ void job_round(const ClassifyParams &p, StageBuf<TILE
     bool liw;
     const uint32_t f = summ_run_flags(__funnelshift_r(lo.x, hi.x, sh) & m, __funnelshift_r(lo.y, hi.y, sh) & m,
                                       __funnelshift_r(lo.z, hi.z, sh), __funnelshift_r(lo.w, hi.w, sh) & m, stop0, wm, liw);
-    const uint32_t wpos = s + hi_bit(wm); // (s - 1 when there is no winner: a harmless load, dropped below)
+    const uint32_t wpos = s + hi_bit(wm | 1u); // (the run's first record when there is no winner: dropped below)
     uint32_t codex = *reinterpret_cast<const uint32_t *>(reinterpret_cast<const uint8_t *>(ctl.codex) + arms[wpos]);
     if (!wm) codex = 0;
     S = Summ{gbase + wpos, summ_run_finish(f, codex, liw)};

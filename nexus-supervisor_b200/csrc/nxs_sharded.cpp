@@ -1,0 +1,305 @@
+// nxs_sharded.cpp — one host batch classified on several GPUs (BASELINE config 3).
+//
+// The unit of dependence of the path is one job = one checkpoint row: superviseAction reads and
+// writes only the row of its (algorithm, id) (services/supervisor.go:264,:301; primary key in
+// test-resources/checkpoints.cql:22), so jobs never interact.  A batch is therefore partitioned on
+// the host by shard = splitmix64(job_key) % G without ever splitting a job, every shard is
+// classified by its own ctx (its own GPU when there are G of them, round-robin otherwise) through
+// the ordinary host-pointer entry point, and the results are put back in stream order on the host —
+// verdicts at the position of their record, job rows in the order in which the jobs end in the
+// stream.  No collective, no peer access: G independent H2D / kernel / D2H pipelines.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <thread>
+#include <vector>
+
+#include "nxs_host.h"
+
+namespace {
+
+struct ShardBuf {
+  nxs_ctx *ctx = nullptr;
+  int device = 0;
+  uint64_t cap = 0; // records the pinned buffers hold
+  uint64_t *key = nullptr;
+  uint16_t *reason = nullptr;
+  uint8_t *kind = nullptr, *flags = nullptr, *stage = nullptr;
+  uint32_t *idx = nullptr; // shard position -> stream position
+  uint32_t *verdict = nullptr;
+  nxs_job_row *rows = nullptr;
+  uint64_t n = 0, n_jobs = 0;
+  int rc = NXS_OK;
+  bool pinned = true; // false only under the CPU test hook (no CUDA runtime to page-lock with)
+};
+
+// How a shard gets classified: nxs_classify on the shard's ctx in the product; the CPU tests of the
+// partition / gather logic plug in their own function (nxs_internal_sharded_run below).
+typedef int (*shard_classify_fn)(void *user, uint32_t shard, const nxs_batch *in, const nxs_out *out);
+
+void free_one(const ShardBuf &b, void *p) {
+  if (b.pinned) nxs_free_host(p);
+  else free(p);
+}
+
+void free_bufs(ShardBuf &b) {
+  free_one(b, b.key);
+  free_one(b, b.reason);
+  free_one(b, b.kind);
+  free_one(b, b.flags);
+  free_one(b, b.stage);
+  free_one(b, b.idx);
+  free_one(b, b.verdict);
+  free_one(b, b.rows);
+  b.key = nullptr, b.reason = nullptr, b.kind = b.flags = b.stage = nullptr;
+  b.idx = b.verdict = nullptr, b.rows = nullptr, b.cap = 0;
+}
+
+int grow_bufs(ShardBuf &b, uint64_t want) {
+  if (want <= b.cap) return NXS_OK;
+  free_bufs(b);
+  const uint64_t cap = (want + want / 16 + 4095) & ~4095ull;
+  void *p[8] = {nullptr};
+  const size_t bytes[8] = {cap * 8, cap * 2, cap, cap, cap, cap * 4, cap * 4, cap * sizeof(nxs_job_row)};
+  for (int i = 0; i < 8; ++i) {
+    if (b.pinned) {
+      if (nxs_alloc_host(bytes[i], &p[i]) != NXS_OK) p[i] = nullptr;
+    } else {
+      p[i] = aligned_alloc(64, (bytes[i] + 63) & ~size_t(63));
+    }
+    if (!p[i]) {
+      for (int j = 0; j < i; ++j) free_one(b, p[j]);
+      return NXS_ERR_NOMEM;
+    }
+  }
+  b.key = static_cast<uint64_t *>(p[0]), b.reason = static_cast<uint16_t *>(p[1]);
+  b.kind = static_cast<uint8_t *>(p[2]), b.flags = static_cast<uint8_t *>(p[3]), b.stage = static_cast<uint8_t *>(p[4]);
+  b.idx = static_cast<uint32_t *>(p[5]), b.verdict = static_cast<uint32_t *>(p[6]);
+  b.rows = static_cast<nxs_job_row *>(p[7]);
+  b.cap = cap;
+  return NXS_OK;
+}
+
+} // namespace
+
+struct nxs_sharded {
+  uint32_t n_shards = 0;
+  uint64_t max_records = 0;
+  std::vector<ShardBuf> shard;
+  unsigned host_threads = 1;
+  char err[256] = {0};
+};
+
+extern "C" {
+
+int nxs_sharded_create(uint32_t n_shards, const int *devices, uint32_t n_devices, uint64_t max_records,
+                       uint16_t finished_mask, nxs_sharded **out) {
+  if (!out) return NXS_ERR_ARG;
+  *out = nullptr;
+  if (n_shards == 0 || n_shards > 256 || !devices || n_devices == 0) return NXS_ERR_ARG;
+  if (max_records == 0 || max_records >= 0xFFFFFFFFull) return NXS_ERR_CAPACITY;
+  nxs_sharded *h = new (std::nothrow) nxs_sharded();
+  if (!h) return NXS_ERR_NOMEM;
+  h->n_shards = n_shards;
+  h->max_records = max_records;
+  h->shard.resize(n_shards);
+  const unsigned hw = std::thread::hardware_concurrency();
+  h->host_threads = hw == 0 ? 4u : hw > 32u ? 32u : hw;
+  for (uint32_t s = 0; s < n_shards; ++s) {
+    h->shard[s].device = devices[s % n_devices];
+    // Any shard may receive (almost) the whole batch: the hash decides, not the size.
+    const int rc = nxs_create(h->shard[s].device, max_records, finished_mask, &h->shard[s].ctx);
+    if (rc != NXS_OK) {
+      nxs_sharded_destroy(h);
+      return rc;
+    }
+  }
+  *out = h;
+  return NXS_OK;
+}
+
+void nxs_sharded_destroy(nxs_sharded *h) {
+  if (!h) return;
+  for (ShardBuf &b : h->shard) {
+    nxs_destroy(b.ctx);
+    free_bufs(b);
+  }
+  delete h;
+}
+
+const char *nxs_sharded_last_error(const nxs_sharded *h) { return h ? h->err : ""; }
+
+static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_out *out, shard_classify_fn classify,
+                                 void *user);
+
+static int classify_on_ctx(void *user, uint32_t shard, const nxs_batch *in, const nxs_out *out) {
+  return nxs_classify(static_cast<nxs_sharded *>(user)->shard[shard].ctx, in, out);
+}
+
+int nxs_classify_sharded(nxs_sharded *h, const nxs_batch *in, const nxs_out *out) {
+  return classify_sharded_impl(h, in, out, classify_on_ctx, h);
+}
+
+// Test hook (not in the public header): the partition and gather of nxs_classify_sharded around a
+// caller-supplied per-shard classifier, without any GPU — `pytest -m "not gpu"` runs the product's
+// host logic with the oracle standing in for the kernel.
+int nxs_internal_sharded_run(uint32_t n_shards, const nxs_batch *in, const nxs_out *out, shard_classify_fn classify,
+                             void *user) {
+  if (n_shards == 0 || n_shards > 256 || !classify) return NXS_ERR_ARG;
+  nxs_sharded h;
+  h.n_shards = n_shards;
+  h.max_records = 0xFFFFFFFEull;
+  h.shard.resize(n_shards);
+  for (ShardBuf &b : h.shard) b.pinned = false;
+  h.host_threads = 3; // more chunks than one, fewer than the shards of some tests
+  const int rc = classify_sharded_impl(&h, in, out, classify, user);
+  for (ShardBuf &b : h.shard) free_bufs(b);
+  return rc;
+}
+
+static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_out *out, shard_classify_fn classify,
+                                 void *user) {
+  if (!h || !in || !out || !out->n_jobs) return NXS_ERR_ARG;
+  const uint64_t n = in->n;
+  if (n > h->max_records) return NXS_ERR_CAPACITY;
+  if (n == 0) {
+    *out->n_jobs = 0;
+    return NXS_OK;
+  }
+  if (!in->kind || !in->reason_id || !in->flags || !in->cur_stage || !in->job_key || !out->verdict || !out->job_rows) {
+    snprintf(h->err, sizeof h->err, "null column pointer");
+    return NXS_ERR_ARG;
+  }
+  const uint32_t G = h->n_shards;
+  const uint64_t *key = in->job_key;
+
+  // ---- host chunks, cut on job boundaries, for the parallel partition and gather
+  const uint64_t chunk_min = h->shard[0].pinned ? (1u << 16) : 64u; // (tiny chunks only under the CPU test hook)
+  const unsigned T = (unsigned)std::min<uint64_t>(h->host_threads, (n + chunk_min - 1) / chunk_min);
+  std::vector<uint64_t> cut(T + 1);
+  cut[0] = 0;
+  cut[T] = n;
+  for (unsigned t = 1; t < T; ++t) {
+    uint64_t i = std::max(cut[t - 1], n * t / T);
+    while (i < n && i > 0 && key[i] == key[i - 1]) ++i;
+    cut[t] = i;
+  }
+  // per chunk and shard: records and jobs
+  std::vector<uint64_t> rec_cnt((size_t)T * G, 0), job_cnt((size_t)T * G, 0);
+  auto parallel = [&](auto &&fn) {
+    std::vector<std::thread> th;
+    for (unsigned t = 1; t < T; ++t) th.emplace_back(fn, t);
+    fn(0u);
+    for (std::thread &x : th) x.join();
+  };
+  parallel([&](unsigned t) {
+    uint64_t *rc = &rec_cnt[(size_t)t * G], *jc = &job_cnt[(size_t)t * G];
+    for (uint64_t i = cut[t]; i < cut[t + 1];) {
+      const uint64_t k = key[i];
+      uint64_t j = i + 1;
+      while (j < cut[t + 1] && key[j] == k) ++j;
+      const uint32_t s = nxs_shard_of(k, G);
+      rc[s] += j - i;
+      jc[s] += 1;
+      i = j;
+    }
+  });
+  // exclusive prefix over the chunks, per shard
+  std::vector<uint64_t> rec_off((size_t)T * G), job_off((size_t)T * G), chunk_job0(T + 1, 0);
+  for (uint32_t s = 0; s < G; ++s) {
+    uint64_t r = 0, j = 0;
+    for (unsigned t = 0; t < T; ++t) {
+      rec_off[(size_t)t * G + s] = r;
+      job_off[(size_t)t * G + s] = j;
+      r += rec_cnt[(size_t)t * G + s];
+      j += job_cnt[(size_t)t * G + s];
+    }
+    h->shard[s].n = r;
+    h->shard[s].n_jobs = j;
+    const int rc = grow_bufs(h->shard[s], r);
+    if (rc != NXS_OK) {
+      snprintf(h->err, sizeof h->err, "cannot allocate pinned staging for shard %u (%llu records)", s, (unsigned long long)r);
+      return rc;
+    }
+  }
+  for (unsigned t = 0; t < T; ++t) {
+    uint64_t j = 0;
+    for (uint32_t s = 0; s < G; ++s) j += job_cnt[(size_t)t * G + s];
+    chunk_job0[t + 1] = chunk_job0[t] + j;
+  }
+  const uint64_t total_jobs = chunk_job0[T];
+
+  // ---- partition: every shard's records in stream order
+  parallel([&](unsigned t) {
+    std::vector<uint64_t> w(rec_off.begin() + (size_t)t * G, rec_off.begin() + (size_t)(t + 1) * G);
+    for (uint64_t i = cut[t]; i < cut[t + 1];) {
+      const uint64_t k = key[i];
+      uint64_t j = i + 1;
+      while (j < cut[t + 1] && key[j] == k) ++j;
+      ShardBuf &b = h->shard[nxs_shard_of(k, G)];
+      uint64_t &pos = w[&b - h->shard.data()];
+      const uint64_t m = j - i;
+      for (uint64_t q = 0; q < m; ++q) b.key[pos + q] = k;
+      memcpy(b.reason + pos, in->reason_id + i, m * 2);
+      memcpy(b.kind + pos, in->kind + i, m);
+      memcpy(b.flags + pos, in->flags + i, m);
+      memcpy(b.stage + pos, in->cur_stage + i, m);
+      for (uint64_t q = 0; q < m; ++q) b.idx[pos + q] = (uint32_t)(i + q);
+      pos += m;
+      i = j;
+    }
+  });
+
+  // ---- classify: one thread per shard, each on its own ctx (and GPU), then scatter its verdicts
+  {
+    std::vector<std::thread> th;
+    auto run = [&](uint32_t s) {
+      ShardBuf &b = h->shard[s];
+      b.rc = NXS_OK;
+      if (b.n == 0) return;
+      nxs_batch sin{b.kind, b.reason, b.flags, b.stage, b.key, b.n};
+      uint64_t jobs = 0;
+      nxs_out sout{b.verdict, b.rows, &jobs};
+      b.rc = classify(user, s, &sin, &sout);
+      if (b.rc != NXS_OK) return;
+      if (jobs != b.n_jobs) {
+        b.rc = NXS_ERR_CUDA;
+        return;
+      }
+      uint32_t *v = out->verdict;
+      for (uint64_t q = 0; q < b.n; ++q) v[b.idx[q]] = b.verdict[q];
+    };
+    for (uint32_t s = 1; s < G; ++s) th.emplace_back(run, s);
+    run(0);
+    for (std::thread &x : th) x.join();
+  }
+  for (uint32_t s = 0; s < G; ++s)
+    if (h->shard[s].rc != NXS_OK) {
+      snprintf(h->err, sizeof h->err, "shard %u on device %d: %s: %s", s, h->shard[s].device, nxs_strerror(h->shard[s].rc),
+               h->shard[s].ctx ? nxs_last_error(h->shard[s].ctx) : "");
+      return h->shard[s].rc;
+    }
+
+  // ---- gather the job rows: jobs in the order in which they end in the stream; a shard's rows are
+  // already in that order among themselves, so row j of the stream is the next unread row of its shard
+  parallel([&](unsigned t) {
+    std::vector<uint64_t> r(job_off.begin() + (size_t)t * G, job_off.begin() + (size_t)(t + 1) * G);
+    nxs_job_row *dst = out->job_rows + chunk_job0[t];
+    for (uint64_t i = cut[t]; i < cut[t + 1];) {
+      const uint64_t k = key[i];
+      uint64_t j = i + 1;
+      while (j < cut[t + 1] && key[j] == k) ++j;
+      const ShardBuf &b = h->shard[nxs_shard_of(k, G)];
+      nxs_job_row row = b.rows[r[&b - h->shard.data()]++];
+      if (row.winner_idx != NXS_NO_WINNER) row.winner_idx = b.idx[row.winner_idx];
+      *dst++ = row;
+      i = j;
+    }
+  });
+  *out->n_jobs = total_jobs;
+  return NXS_OK;
+}
+
+} // extern "C"

@@ -75,3 +75,49 @@ def test_partition_keeps_jobs_whole_and_ordered():
             assert np.array_equal(c[k], want[k])
     sizes = np.array([len(idx) for _, idx in parts])
     assert sizes.max() / sizes.mean() < 1.05
+
+
+@pytest.mark.parametrize("G", [1, 2, 3, 8])
+def test_product_partition_and_gather_with_the_oracle_as_classifier(G):
+    """The host logic of nxs_classify_sharded itself (C++: parallel partition on job boundaries, per-shard
+    classification, verdict scatter, job-row merge with winner indices translated back), run on the CPU
+    through the library's test hook with the oracle standing in for the kernel, against one unsharded
+    oracle run."""
+    import ctypes as C
+    import nexus_supervisor_b200 as nx
+    from oracle import cpu_oracle
+    lib = nx._abi.load()
+    FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_uint32, C.POINTER(nx._abi.Batch), C.POINTER(nx._abi.Out))
+    lib.nxs_internal_sharded_run.restype = C.c_int
+    lib.nxs_internal_sharded_run.argtypes = [C.c_uint32, C.POINTER(nx._abi.Batch), C.POINTER(nx._abi.Out), FN, C.c_void_p]
+    seen = {}
+
+    def classify_shard(user, shard, bp, op):
+        b, o = bp.contents, op.contents
+        n = b.n
+
+        def arr(ptr, dt):
+            return np.frombuffer((C.c_uint8 * (n * np.dtype(dt).itemsize)).from_address(ptr), dtype=dt)
+        cols = {"kind": arr(b.kind, np.uint8), "reason_id": arr(b.reason_id, np.uint16), "flags": arr(b.flags, np.uint8),
+                "cur_stage": arr(b.cur_stage, np.uint8), "job_key": arr(b.job_key, np.uint64)}
+        assert all(nx.shard_of(int(k), G) == shard for k in cols["job_key"][:20])
+        v, r = cpu_oracle.classify(cols)
+        arr(o.verdict, np.uint32)[:] = v
+        np.frombuffer((C.c_uint8 * (16 * len(r))).from_address(o.job_rows), dtype=cpu_oracle.JOB_ROW)[:] = r
+        C.c_uint64.from_address(o.n_jobs).value = len(r)
+        seen[shard] = n
+        return 0
+
+    rng = np.random.default_rng(G)
+    for n, max_len in ((1, 1), (777, 3), (40_000, 6), (30_001, 900)):
+        cols = util.random_cols(rng, n, max_len)
+        verdict = np.zeros(n, np.uint32)
+        rows = np.zeros(n, cpu_oracle.JOB_ROW)
+        nj = C.c_uint64(0)
+        batch = nx._abi.Batch(cols["kind"].ctypes.data, cols["reason_id"].ctypes.data, cols["flags"].ctypes.data,
+                              cols["cur_stage"].ctypes.data, cols["job_key"].ctypes.data, n)
+        out = nx._abi.Out(verdict.ctypes.data, rows.ctypes.data, C.addressof(nj))
+        seen.clear()
+        assert lib.nxs_internal_sharded_run(G, C.byref(batch), C.byref(out), FN(classify_shard), None) == 0
+        assert sum(seen.values()) == n
+        util.assert_same(verdict, rows[:nj.value], *cpu_oracle.classify(cols), f"G={G} n={n}")
