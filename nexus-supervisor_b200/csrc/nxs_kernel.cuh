@@ -5,26 +5,24 @@
 // the records of each job into one row.  Each CTA is a warp-specialised pipeline
 // over a ring of shared-memory stages, driven by mbarriers only:
 //
-//   producer warp   claims a tile id from a global counter when a stage is about to be
-//                   free and streams the five input columns of the tile into the stage
-//                   with 1-D bulk async copies (TMA engine, SASS UBLKCP)
-//   counter warps   (eight) as soon as a tile has landed each marks an eighth of it:
-//                   compares the adjacent job keys, leaves the "last record of a job"
-//                   bit masks and the jobs-per-range offsets in the stage; the tile's
-//                   owner among them (they take the tiles in turn) publishes the tile's
-//                   JOB COUNT, polls predecessor tiles (decoupled look-back on counts
-//                   only) for the index of the tile's first job row and releases the workers
-//   worker warps    each warp owns a contiguous range of the tile and makes two passes
-//                   over it.  Record pass, 32 records at a time, lane per record:
-//                   table lookups -> packed verdict -> global; five warp ballots
-//                   -> one row of bit masks per 32 records, kept in the stage in
-//                   place of the columns just consumed, as are the switch arm of
+//   producer warp   claims a tile id from a global counter when a stage is about to be free and
+//                   streams the five input columns of the tile into the stage with 1-D bulk async
+//                   copies (TMA engine, SASS UBLKCP); the keys land on their own barrier
+//   worker warps    each warp owns a contiguous range of the tile and makes three passes over it.
+//                   Marking, as soon as the keys have landed: adjacent keys compared, the "last
+//                   record of a job" bit masks and the range's job count left in the stage.
+//                   Record pass, 32 records at a time, lane per record: table lookups -> packed
+//                   verdict -> global; four warp ballots -> one row of bit masks per 32 records, kept
+//                   in the stage in place of the columns just consumed, as are the switch arm of
 //                   every record and the list of the positions where jobs end.
-//                   Job pass, lane per JOB: a lane cuts its job's bits out of the
-//                   mask rows with funnel shifts, folds them with a dozen bit
-//                   operations and stores the 16-byte job row at its final
-//                   position — every lane does useful work, whatever the share of
-//                   records that end a job
+//                   Job pass, lane per JOB, once the index of the tile's first job row is known: a
+//                   lane cuts its job's bits out of the mask rows with funnel shifts, folds them with
+//                   a dozen bit operations and stores the 16-byte job row at its final position —
+//                   every lane does useful work, whatever the share of records that end a job
+//   look-back warps (they take the tiles in turn) when a tile is marked: add up the ranges' job
+//                   counts, publish the tile's JOB COUNT, poll predecessor tiles (decoupled look-back
+//                   on counts only) for the index of the tile's first job row — all of it while the
+//                   workers run the record pass
 //   summary warp    after the workers: frees the stage, publishes the summary of
 //                   the job left open at the tile's end, and writes the few rows
 //                   the workers could not close — jobs that began before a
@@ -32,9 +30,8 @@
 //                   off-the-critical-path look-back on summaries)
 //
 // Splitting the look-back in two keeps the stage's residency short: the count is
-// known as soon as the keys have landed, so row positions are ready before the
-// expensive pass starts and no stage waits for another CTA's classification.
-// The worker warps run nothing but the classification pass and wait on one barrier.
+// known as soon as the keys have landed and been compared, so the count look-back
+// runs beside the record pass and no stage waits for another CTA's classification.
 // Scratch: TileDesc[n_tiles] (16 B each) + 3 counters.
 #pragma once
 #include "nxs_device.cuh"
@@ -50,10 +47,15 @@ constexpr int kProducerWarp = kWorkerWarps;
 constexpr int kSummaryWarp = kWorkerWarps + 1;
 constexpr int kCounterWarp0 = kWorkerWarps + 2; // first of kCounterWarps counter warps
 #ifndef NXS_COUNTER_WARPS
-#define NXS_COUNTER_WARPS 8
+#define NXS_COUNTER_WARPS 2
 #endif
-constexpr int kCounterWarps = NXS_COUNTER_WARPS; // tile k of a CTA is counted and looked up by counter warp k % kCounterWarps
-constexpr int kThreads = kWorkers + 64 + 32 * kCounterWarps;
+constexpr int kCounterWarps = NXS_COUNTER_WARPS; // look-back warps: tile k of a CTA is looked up by warp k % kCounterWarps
+#ifndef NXS_MARKER_WARPS
+#define NXS_MARKER_WARPS 8
+#endif
+constexpr int kMarkerWarps = NXS_MARKER_WARPS; // each marks the job boundaries of its share of the worker ranges of every tile
+constexpr int kMarkerWarp0 = kCounterWarp0 + kCounterWarps;
+constexpr int kThreads = kWorkers + 64 + 32 * (kCounterWarps + kMarkerWarps);
 constexpr int kPendingSlots = 4;                // tiles whose carried-in summary is still being looked up
 constexpr uint64_t kWatchdogNs = 8000000000ull; // a stuck wait traps instead of hanging the GPU
 
@@ -102,21 +104,22 @@ template <int TILE> struct __align__(128) StageBuf {
   // The four small columns are consumed by the record pass of a worker range and then reused IN PLACE,
   // range by range, for what the job pass reads (a range = RANGE records of one worker warp):
   //   reason[r0 + q]            <- u16: position + 1 (range-local) of the q-th record that ends a job
-  //   kind[r0 + i]              <- u8: 4 * switch arm of record i
+  //   kind[r0 + i]              <- u8: 4 * switch arm | 32 * gate class | 128 * IsFinished(cur_stage) of record i
   //   flags[r0 + 16 c .. +15]   <- MaskRow of 32-record chunk c of the range (he, tm, fl, er ballots)
   // (every write lands on bytes of records the pass has already read: q <= i, 16 c <= 32 c; stage stays)
   uint16_t reason[TILE];
   uint8_t kind[TILE];
   alignas(16) uint8_t flags[TILE];
   alignas(16) uint8_t stage[TILE];
-  uint2 tailinfo[TILE / 32]; // .x bit b: record 32*chunk + b is the last of its job; .y: jobs ending earlier in the worker range
+  uint2 tailinfo[TILE / 32]; // .x bit b: record 32*chunk + b is the last of its job; .y: shared-memory address of the
+                             //   list entry (see reason[]) of the first job that ends in the chunk
   RangeInfo range[kWorkerWarps];
-  uint32_t range_off[kWorkerWarps]; // jobs ending before each range, tile-local
-  uint32_t part_total[kCounterWarps]; // jobs ending in each counter warp's part of the tile
-  uint32_t tile_base;               // job rows before the tile
-  uint32_t first_is_head;           // the tile's first record begins a job
-  int32_t tile;                     // tile id, -1 = end of work
-  uint32_t total;                   // jobs ending in the tile
+  uint32_t range_cnt[kWorkerWarps]; // jobs ending in each range                        (marker warps)
+  uint32_t range_row[kWorkerWarps]; // index of the first job row of each range        (look-back warp)
+  uint32_t tile_base;               // job rows before the tile                        (look-back warp)
+  uint32_t first_is_head;           // the tile's first record begins a job            (marker warp 0)
+  int32_t tile;                     // tile id, -1 = end of work                       (producer)
+  uint32_t total;                   // jobs ending in the tile                         (look-back warp)
 };
 
 // Verdict table entry = packed verdict of the record plus the fold bits above it.
@@ -137,10 +140,10 @@ struct PendingTile {
 };
 
 template <int STAGES> struct Ctl {
-  uint64_t full[STAGES];       // the tile's keys landed    (producer -> counter warps)
+  uint64_t full[STAGES];       // the tile's keys landed    (producer -> marker warps)
   uint64_t cols[STAGES];       // its other columns landed  (producer -> workers)
-  uint64_t marked[STAGES];     // job boundaries marked    (counter warps -> the tile's owner among them)
-  uint64_t base_ready[STAGES]; // first row index known    (counter warp -> workers)
+  uint64_t marked[STAGES];     // job boundaries marked    (marker warps -> look-back warps, workers)
+  uint64_t base_ready[STAGES]; // first row index known    (look-back warp -> workers)
   uint64_t p1done[STAGES];     // rows written             (workers -> summary warp)
   uint64_t freeb[STAGES];      // stage reusable           (summary warp -> producer)
   PendingTile pending[kPendingSlots];
@@ -358,42 +361,37 @@ __device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<
   }
 }
 
-// ------------------------------------------------------- job boundaries (counter warps)
-// Every counter warp marks one part of a landed tile (part q = worker ranges q*RPP ..): the
-// "last record of its job" bit masks, the number of jobs ending before each of its ranges
-// (relative to the part) and the part's job count; part 0 also notes whether the tile's first
-// record begins a job.  A ragged (last) tile is read from global memory here and copied into
-// the stage for the classification pass.
-template <int TILE>
-__device__ __forceinline__ void count_part(const ClassifyParams &p, StageBuf<TILE> &sb, uint32_t tile, uint32_t part,
+// ------------------------------------------------------- job boundaries (marker warps)
+// As soon as the keys of a tile have landed the marker warps mark it, each its share of the worker
+// ranges: per range (`warp` = the worker warp that owns it) the "last record of its job" bit mask of
+// every 32-record chunk, with the place in the job-end list where the chunk's first entry goes, and
+// the number of jobs that end in the range; range 0 also notes whether the tile's first record begins a
+// job.  They do nothing else and never wait for anything but the landing, so the tile's job count —
+// which every later tile of the grid waits for — is known a fixed, short time after the load.  A
+// ragged (last) tile is read from global memory here and copied into the stage for the other passes.
+template <int TILE, bool FULL>
+__device__ __forceinline__ void mark_range(const ClassifyParams &p, StageBuf<TILE> &sb, uint32_t tile, uint32_t warp,
                                            uint32_t lane) {
-  static_assert(kWorkerWarps % kCounterWarps == 0, "the worker ranges are split evenly among the counter warps");
-  constexpr uint32_t RANGE = TILE / kWorkerWarps, CPW = RANGE / 32, RPP = kWorkerWarps / kCounterWarps;
-  const uint32_t start = tile * TILE;
-  const uint32_t cnt = min((uint32_t)TILE, p.n - start);
-  uint32_t total = 0;
-  if (cnt == (uint32_t)TILE) {
-    const bool last_tile = start + cnt == p.n;
-#pragma unroll 1
-    for (uint32_t r = part * RPP; r < (part + 1) * RPP; ++r) {
-      uint32_t jobs = 0;
+  constexpr uint32_t RANGE = TILE / kWorkerWarps, CPW = RANGE / 32;
+  const uint32_t start = tile * TILE, r0 = warp * RANGE;
+  const uint32_t ends_a = smem_u32(sb.reason + r0); // job-end list of the range (see StageBuf)
+  uint32_t jobs = 0;
+  if (FULL) {
+    const bool last_tile = start + TILE == p.n;
 #pragma unroll
-      for (uint32_t j = 0; j < CPW; ++j) {
-        const uint32_t i = r * RANGE + j * 32 + lane;
-        bool tail = sb.keyx[2 + i] != sb.keyx[3 + i];
-        if (last_tile && i == TILE - 1) tail = true;
-        const uint32_t T = __ballot_sync(0xffffffffu, tail);
-        if (lane == 0) sb.tailinfo[r * CPW + j] = make_uint2(T, jobs);
-        jobs += __popc(T);
-      }
-      if (lane == 0) sb.range_off[r] = total;
-      total += jobs;
+    for (uint32_t j = 0; j < CPW; ++j) {
+      const uint32_t i = r0 + j * 32 + lane;
+      bool tail = sb.keyx[2 + i] != sb.keyx[3 + i];
+      if (last_tile && i == TILE - 1) tail = true;
+      const uint32_t T = __ballot_sync(0xffffffffu, tail);
+      if (lane == 0) sb.tailinfo[r0 / 32 + j] = make_uint2(T, ends_a + 2u * jobs);
+      jobs += __popc(T);
     }
-    if (part == 0 && lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(sb.keyx[2] != sb.keyx[1]);
+    if (warp == 0 && lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(sb.keyx[2] != sb.keyx[1]);
   } else { // ragged last tile (once per launch)
-    uint32_t range_start = 0; // `total` at the first chunk of the current worker range
-    for (uint32_t c = part * RPP * CPW; c < (part + 1) * RPP * CPW; ++c) {
-      const uint32_t i = c * 32 + lane;
+    const uint32_t cnt = p.n - start;
+    for (uint32_t j = 0; j < CPW; ++j) {
+      const uint32_t i = r0 + j * 32 + lane;
       bool tail = false;
       if (i < cnt) {
         const uint64_t key = p.key[start + i];
@@ -405,16 +403,12 @@ __device__ __forceinline__ void count_part(const ClassifyParams &p, StageBuf<TIL
         sb.stage[i] = p.stage[start + i];
       }
       const uint32_t T = __ballot_sync(0xffffffffu, tail);
-      if (c % CPW == 0) range_start = total;
-      if (lane == 0) {
-        if (c % CPW == 0) sb.range_off[c / CPW] = total;
-        sb.tailinfo[c] = make_uint2(T, total - range_start);
-      }
-      total += __popc(T);
+      if (lane == 0) sb.tailinfo[r0 / 32 + j] = make_uint2(T, ends_a + 2u * jobs);
+      jobs += __popc(T);
     }
-    if (part == 0 && lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(p.key[start] != p.key[start - 1]);
+    if (warp == 0 && lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(p.key[start] != p.key[start - 1]);
   }
-  if (lane == 0) sb.part_total[part] = total;
+  if (lane == 0) sb.range_cnt[warp] = jobs;
 }
 
 // ----------------------------------------------------------------- counter warp
@@ -455,66 +449,85 @@ __device__ __forceinline__ bool count_lookback_poll(const ClassifyParams &p, Cou
   return false;
 }
 
-// The counter warps of a CTA share the marking of every tile (each takes a part, see count_part) and
-// take the tiles in turn for the rest: counter warp `which` OWNS the tiles k = which, which +
-// kCounterWarps, ... (k = order in which the CTA claimed them); the owner adds up the parts, publishes
-// the tile's job count and runs the look-back, so that several look-backs are in flight per CTA: one
-// look-back costs a few L2 round trips, more than the time a tile may take at full speed.  Each warp is
-// an event loop with this order of duties: mark a freshly landed tile, publish the count of an own
-// tile that is fully marked, poll for the oldest own tile — every later tile of every CTA waits for the
-// counts.  Every counter warp watches every use of every `full` barrier in order and arrives on
-// `marked` itself before it waits there, so no parity wait can mistake a phase for the one two before.
 template <int TILE, int STAGES>
-__device__ __forceinline__ void counter_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
-                                             uint32_t which, uint32_t lane) {
-  constexpr uint32_t RPP = kWorkerWarps / kCounterWarps;
-  uint32_t km = 0;                 // next tile of the CTA to mark (all of them, in order)
-  uint32_t kf = which, kl = which; // next own tile to publish the count of / to look back for
-  uint32_t k_end = 0xFFFFFFFFu;    // index of the end marker, once seen
+__device__ __forceinline__ void marker_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
+                                            uint32_t which, uint32_t lane) {
+  static_assert(kWorkerWarps % kMarkerWarps == 0, "the worker ranges are split evenly among the marker warps");
+  constexpr uint32_t RPP = kWorkerWarps / kMarkerWarps;
+  Watchdog wd;
+  for (uint32_t k = 0;; ++k) {
+    const uint32_t s = k % STAGES;
+    while (!__all_sync(0xffffffffu, mbar_try_wait(&ctl.full[s], (k / STAGES) & 1u, 2000u))) wd.tick(p.counters + 2);
+    wd.reset();
+    StageBuf<TILE> &sb = stages[s];
+    const int32_t t = sb.tile;
+    if (t >= 0) {
+      if (which == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_COUNT_START, (uint32_t)t);
+      const bool full_tile = p.n - (uint32_t)t * TILE >= (uint32_t)TILE;
+#pragma unroll 1
+      for (uint32_t r = which * RPP; r < (which + 1) * RPP; ++r) {
+        if (full_tile) mark_range<TILE, true>(p, sb, (uint32_t)t, r, lane);
+        else mark_range<TILE, false>(p, sb, (uint32_t)t, r, lane);
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&ctl.marked[s]);
+    if (t < 0) break;
+  }
+}
+
+// The look-back warps of a CTA take its tiles in turn: warp `which` OWNS the tiles k = which, which +
+// kCounterWarps, ... (k = order in which the CTA claimed them), so that several look-backs are in flight
+// per CTA: one look-back costs a few L2 round trips, more than the time a tile may take at full speed.
+// When the marker warps are done with an own tile, the warp adds up the ranges' job counts, publishes the
+// tile's job count — every later tile of every CTA waits for the counts — and then polls predecessor
+// counts for the index of the tile's first job row, which the workers need for the job pass only.
+// Each warp is an event loop: pass over the tiles of the CTA in order (publishing on the way), poll for
+// the oldest own tile in between.  Every warp watches every use of every `marked` barrier in order; a
+// stage cannot be marked twice more while a look-back for it is pending (its next use needs the stage
+// back, which needs this look-back), so no parity wait can mistake a phase for the one two before.
+template <int TILE, int STAGES>
+__device__ __forceinline__ void lookback_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
+                                              uint32_t which, uint32_t lane) {
+  uint32_t km = 0;              // next tile of the CTA whose marking to await (all of them, in order)
+  uint32_t kl = which;          // next own tile to look back for
+  uint32_t k_end = 0xFFFFFFFFu; // index of the end marker, once seen
   bool lb_active = false;
   CountLookback st{0, 0u};
   Watchdog wd;
   while (true) {
     const uint32_t sm = km % STAGES;
-    if (k_end == 0xFFFFFFFFu && __all_sync(0xffffffffu, mbar_test_wait(&ctl.full[sm], (km / STAGES) & 1u))) {
+    if (k_end == 0xFFFFFFFFu && __all_sync(0xffffffffu, mbar_test_wait(&ctl.marked[sm], (km / STAGES) & 1u))) {
       StageBuf<TILE> &sb = stages[sm];
       const int32_t t = sb.tile;
       if (t < 0) {
         k_end = km;
       } else {
-        if (lane == 0 && km % kCounterWarps == which) NXS_TRACE_EVENT(p, EV_COUNT_START, (uint32_t)t);
-        count_part<TILE>(p, sb, (uint32_t)t, which, lane);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&ctl.marked[sm]);
+        if (km % kCounterWarps == which) { // own tile: job rows before each range, the tile's count
+          const uint32_t tile = (uint32_t)t;
+          const uint32_t c = lane < (uint32_t)kWorkerWarps ? sb.range_cnt[lane] : 0u;
+          uint32_t incl = c;
+#pragma unroll
+          for (int d = 1; d < kWorkerWarps; d <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
+            if ((int)lane >= d) incl += v;
+          }
+          const uint32_t total = __shfl_sync(0xffffffffu, incl, kWorkerWarps - 1);
+          if (lane < (uint32_t)kWorkerWarps) sb.range_row[lane] = incl - c; // tile-local until the look-back is done
+          if (lane == 0) {
+            sb.total = total;
+            st_desc_word(&p.desc[tile].c, desc_c(total, tile == 0 ? DESC_INC : DESC_AGG, p.gen));
+            if (p.n_tiles == 1) *p.n_jobs = total;
+            NXS_TRACE_EVENT(p, EV_COUNT_END, tile);
+          }
+          __syncwarp();
+        }
         ++km;
       }
       wd.reset();
       continue;
     }
-    if (kf < km && __all_sync(0xffffffffu, mbar_test_wait(&ctl.marked[kf % STAGES], (kf / STAGES) & 1u))) {
-      StageBuf<TILE> &sb = stages[kf % STAGES];
-      const uint32_t tile = (uint32_t)sb.tile;
-      // job rows before each part, then before each range, of the tile
-      uint32_t before = 0, total = 0;
-#pragma unroll
-      for (uint32_t q = 0; q < (uint32_t)kCounterWarps; ++q) {
-        const uint32_t c = sb.part_total[q];
-        if (q < lane / RPP) before += c;
-        total += c;
-      }
-      if (lane < (uint32_t)kWorkerWarps && before) sb.range_off[lane] += before;
-      if (lane == 0) {
-        sb.total = total;
-        st_desc_word(&p.desc[tile].c, desc_c(total, tile == 0 ? DESC_INC : DESC_AGG, p.gen));
-        if (p.n_tiles == 1) *p.n_jobs = total;
-        NXS_TRACE_EVENT(p, EV_COUNT_END, tile);
-      }
-      __syncwarp();
-      kf += kCounterWarps;
-      wd.reset();
-      continue;
-    }
-    if (kl < kf) { // look up the first row index of the oldest own tile (one round trip per poll)
+    if (kl < km) { // look up the first row index of the oldest own tile (one round trip per poll)
       const uint32_t sl = kl % STAGES;
       StageBuf<TILE> &sb = stages[sl];
       const uint32_t tile = (uint32_t)sb.tile;
@@ -525,6 +538,7 @@ __device__ __forceinline__ void counter_loop(const ClassifyParams &p, StageBuf<T
       }
       if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_POLL, tile);
       if (tile == 0 || count_lookback_poll(p, st, lane)) {
+        if (lane < (uint32_t)kWorkerWarps) sb.range_row[lane] += st.excl;
         if (lane == 0) {
           const uint32_t total = sb.total;
           if (tile != 0) st_desc_word(&p.desc[tile].c, desc_c(st.excl + total, DESC_INC, p.gen));
@@ -543,14 +557,10 @@ __device__ __forceinline__ void counter_loop(const ClassifyParams &p, StageBuf<T
       wd.tick(p.counters + 2);
       continue;
     }
-    if (k_end != 0xFFFFFFFFu && kf >= k_end) { // every own tile is done (kl == kf here)
-      // the end marker takes a turn like a tile: its owner wakes the workers
-      if (k_end % kCounterWarps == which && lane == 0) mbar_arrive(&ctl.base_ready[k_end % STAGES]);
-      break;
-    }
-    // nothing to do: wait for the next tile to land, or for the partners to finish marking an own one
-    if (k_end == 0xFFFFFFFFu && kf >= km) {
-      if (!__all_sync(0xffffffffu, mbar_try_wait(&ctl.full[sm], (km / STAGES) & 1u, 2000u))) aux_nap<NXS_COUNTER_NS>();
+    if (k_end != 0xFFFFFFFFu && kl >= k_end) break; // every own tile is done
+    // nothing to do: wait for the next tile to be marked
+    if (k_end == 0xFFFFFFFFu) {
+      if (!__all_sync(0xffffffffu, mbar_try_wait(&ctl.marked[sm], (km / STAGES) & 1u, 2000u))) aux_nap<NXS_COUNTER_NS>();
     }
     wd.tick(p.counters + 2);
   }
@@ -592,7 +602,7 @@ __device__ __noinline__ Summ long_run(const StageBuf<TILE> &sb, const Ctl<STAGES
     uint32_t codex = 0, wpos = pos;
     if (wm) {
       wpos = pos + hi_bit(wm);
-      codex = ctl.codex[arms[wpos] >> 2];
+      codex = ctl.codex[(arms[wpos] >> 2) & 7u];
     }
     S = summ_combine(S, Summ{gbase + wpos, summ_run_finish(f, codex, liw)});
     pos += take;
@@ -616,8 +626,9 @@ __device__ __forceinline__ void job_round(const ClassifyParams &p, StageBuf<TILE
   if (FIRST && k == 0) s = 0;
   const uint32_t len = e1 - s;
   const bool anchored = !FIRST || k != 0 || first_is_head;
-  // IsFinished() of the row the job's first record found (:276): a stop before the first record
-  const bool stop0 = anchored && ((p.finished_mask >> (sb.stage[r0 + s] & 15u)) & 1u);
+  // IsFinished() of the row the job's first record found (:276) — bit 7 of the byte the record pass
+  // left for the record: a stop before the first record
+  const bool stop0 = anchored && (arms[s] & 0x80u);
   Summ S;
   if (len <= 32u) {
     const uint32_t w = s >> 5, sh = s & 31u;
@@ -628,7 +639,7 @@ __device__ __forceinline__ void job_round(const ClassifyParams &p, StageBuf<TILE
     const uint32_t f = summ_run_flags(__funnelshift_r(lo.x, hi.x, sh) & m, __funnelshift_r(lo.y, hi.y, sh) & m,
                                       __funnelshift_r(lo.z, hi.z, sh), __funnelshift_r(lo.w, hi.w, sh) & m, stop0, wm, liw);
     const uint32_t wpos = s + hi_bit(wm | 1u); // (the run's first record when there is no winner: dropped below)
-    uint32_t codex = *reinterpret_cast<const uint32_t *>(reinterpret_cast<const uint8_t *>(ctl.codex) + arms[wpos]);
+    uint32_t codex = *reinterpret_cast<const uint32_t *>(reinterpret_cast<const uint8_t *>(ctl.codex) + (arms[wpos] & 0x1Cu));
     if (!wm) codex = 0;
     S = Summ{gbase + wpos, summ_run_finish(f, codex, liw)};
   } else {
@@ -653,50 +664,43 @@ __device__ __forceinline__ void job_round(const ClassifyParams &p, StageBuf<TILE
   }
 }
 
+__device__ __forceinline__ void sts_u16(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)v) : "memory");
+}
+
+// ------------------------------------------------------------------ record pass
+// onEvent: guards (:155,:161,:218) and the (kind, reason) switch arms, then superviseAction's order:
+// no checkpoint (:265) -> finished (:276) -> switch (:283).  All of it is table lookups.
 template <int TILE, bool FULL, int STAGES>
-__device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf<TILE> &sb, const Ctl<STAGES> &ctl,
-                                               uint32_t tile, uint32_t warp, uint32_t lane) {
+__device__ __forceinline__ void record_pass(const ClassifyParams &p, StageBuf<TILE> &sb, const Ctl<STAGES> &ctl,
+                                            uint32_t tile, uint32_t warp, uint32_t lane) {
   static_assert(TILE % (kWorkerWarps * 32 * kRecordGroup) == 0, "a range is a whole number of record groups");
   constexpr uint32_t RANGE = TILE / kWorkerWarps; // records per warp
   constexpr uint32_t CPW = RANGE / 32;            // 32-record chunks per warp
   const uint32_t start = tile * TILE;
   const uint32_t cnt = FULL ? (uint32_t)TILE : p.n - start;
   const uint32_t r0 = warp * RANGE;
-  if (!FULL && r0 >= cnt) { // nothing of the ragged tile falls in this range
-    if (lane == 0) sb.range[warp] = RangeInfo{summ_pack(summ_identity()), 0ull, 0ull, 0u, 0u};
-    return;
-  }
+  if (!FULL && r0 >= cnt) return; // nothing of the ragged tile falls in this range
   const uint32_t cnt_r = FULL ? RANGE : min(RANGE, cnt - r0); // records of the range that exist
-  const uint32_t lt = (1u << lane) - 1u;
-  // Does the first record of the range begin a job?  (warp-uniform)
-  const bool first_is_head = (r0 == 0 ? sb.first_is_head : sb.tailinfo[r0 / 32 - 1].x >> 31) != 0;
-
   // What the job pass reads, written in place of the consumed columns (see StageBuf).
-  uint16_t *const ends = sb.reason + r0;
   uint8_t *const arms = sb.kind + r0;
   MaskRow *const rows_m = reinterpret_cast<MaskRow *>(sb.flags + r0);
-
-  // ------------------------------------------------------------------ record pass
-  // onEvent: guards (:155,:161,:218) and the (kind, reason) switch arms, then superviseAction's order:
-  // no checkpoint (:265) -> finished (:276) -> switch (:283).  All of it is table lookups.
-  uint32_t njobs = 0, last_T = 0;
   uint32_t *pv = p.verdict + (size_t)start + r0 + lane;
 #pragma unroll 1
   for (uint32_t g = 0; g < CPW; g += kRecordGroup, pv += 32 * kRecordGroup) {
-    uint2 ti[kRecordGroup];
-    uint32_t vt[kRecordGroup], arm4[kRecordGroup];
+    uint32_t vt[kRecordGroup], off[kRecordGroup];
     // loads and lookups of the whole group first: the stores below land on bytes read here
 #pragma unroll
     for (uint32_t u = 0; u < kRecordGroup; ++u) {
       const uint32_t i = (g + u) * 32 + lane;
-      ti[u] = sb.tailinfo[r0 / 32 + g + u];
       vt[u] = 0;
-      arm4[u] = 0;
+      off[u] = 0;
       if (FULL || i < cnt_r) {
         const uint32_t kind = sb.kind[r0 + i], reason = sb.reason[r0 + i], fl = sb.flags[r0 + i], st = sb.stage[r0 + i];
-        arm4[u] = ctl.lut[umin32(kind, 3u) * 33u + umin32(reason, 32u)];
+        const uint32_t arm4 = ctl.lut[umin32(kind, 3u) * 33u + umin32(reason, 32u)];
         const uint32_t l2 = ctl.lut2[st * 8u + (fl & 7u)];
-        vt[u] = *reinterpret_cast<const uint32_t *>(reinterpret_cast<const uint8_t *>(ctl.vt) + (arm4[u] + l2));
+        off[u] = arm4 + l2; // 4 * arm | 32 * gate class | 128 * IsFinished(cur_stage): one byte
+        vt[u] = *reinterpret_cast<const uint32_t *>(reinterpret_cast<const uint8_t *>(ctl.vt) + off[u]);
         __stcs(pv + 32 * u, vt[u] & kVerdictMask);
       }
     }
@@ -705,18 +709,44 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
       const uint32_t c = g + u, i = c * 32 + lane;
       const uint32_t HE = ballot_bit(vt[u], VT_HE), TM = ballot_bit(vt[u], VT_TERM);
       const uint32_t FL = ballot_bit(vt[u], VT_FAIL), ER = ballot_bit(vt[u], VT_ERR);
-      if (FULL || i < cnt_r) arms[i] = (uint8_t)arm4[u];
+      if (FULL || i < cnt_r) arms[i] = (uint8_t)off[u];
       if (lane == 0) *reinterpret_cast<uint4 *>(rows_m + c) = make_uint4(HE, TM, FL, ER);
-      const uint32_t T = ti[u].x;
-      if ((T >> lane) & 1u) ends[ti[u].y + __popc(T & lt)] = (uint16_t)(i + 1);
-      if (u == kRecordGroup - 1) njobs = ti[u].y + __popc(T), last_T = T;
     }
   }
-  // Does the range end on a job boundary?  If not, the end of the range closes the list: the run behind
-  // the last job end is the job still open there.  (Then njobs < RANGE, so the entry exists.)
-  const bool closed = FULL ? (last_T >> 31) != 0 : (sb.tailinfo[(r0 + cnt_r - 1) / 32].x >> ((cnt_r - 1) & 31u)) & 1u;
+}
+
+// --------------------------------------------------------------------- job pass (a lane per run)
+template <int TILE, bool FULL, int STAGES>
+__device__ __forceinline__ void job_pass(const ClassifyParams &p, StageBuf<TILE> &sb, const Ctl<STAGES> &ctl,
+                                         uint32_t tile, uint32_t warp, uint32_t lane) {
+  constexpr uint32_t RANGE = TILE / kWorkerWarps;
+  const uint32_t start = tile * TILE;
+  const uint32_t cnt = FULL ? (uint32_t)TILE : p.n - start;
+  const uint32_t r0 = warp * RANGE;
+  if (!FULL && r0 >= cnt) { // nothing of the ragged tile falls in this range
+    if (lane == 0) sb.range[warp] = RangeInfo{summ_pack(summ_identity()), 0ull, 0ull, 0u, 0u};
+    return;
+  }
+  const uint32_t cnt_r = FULL ? RANGE : min(RANGE, cnt - r0);
+  // The list of the positions (+ 1) where jobs end, from the marker warps' bit masks, into the
+  // range's slice of the reason column (consumed by the record pass).
+  {
+    constexpr uint32_t CPW = RANGE / 32;
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (uint32_t j = 0; j < CPW; ++j) {
+      const uint2 ti = sb.tailinfo[r0 / 32 + j];
+      if ((ti.x >> lane) & 1u) sts_u16(ti.y + 2u * __popc(ti.x & lt), j * 32 + lane + 1);
+    }
+  }
+  const uint32_t njobs = sb.range_cnt[warp];
+  // Does the first record of the range begin a job, does its last record end one?  (warp-uniform)
+  const bool first_is_head = (r0 == 0 ? sb.first_is_head : sb.tailinfo[r0 / 32 - 1].x >> 31) != 0;
+  const bool closed = (sb.tailinfo[(r0 + cnt_r - 1) / 32].x >> ((cnt_r - 1) & 31u)) & 1u;
+  // If the range does not end on a job boundary, the end of the range closes the job-end list: the run
+  // behind the last job end is the job still open there.  (Then njobs < RANGE, so the entry exists.)
   if (lane == 0) {
-    if (!closed) ends[njobs] = (uint16_t)cnt_r;
+    if (!closed) sb.reason[r0 + njobs] = (uint16_t)cnt_r;
     else { // nothing flows out of the range
       sb.range[warp].suffix = summ_pack(Summ{0u, F_ANCHORED});
       sb.range[warp].flags = RANGE_CLOSED | (first_is_head ? RANGE_FIRST_IS_HEAD : 0u);
@@ -724,11 +754,9 @@ __device__ __forceinline__ void classify_range(const ClassifyParams &p, StageBuf
     }
   }
   __syncwarp();
-
-  // --------------------------------------------------------------------- job pass (a lane per run)
   const uint32_t nruns = njobs + (closed ? 0u : 1u);
   const uint32_t gbase = p.record_base + start + r0; // batch index of the range's first record
-  nxs_job_row *prow = p.rows + ((size_t)sb.tile_base + sb.range_off[warp] + lane); // row of run `lane`
+  nxs_job_row *prow = p.rows + ((size_t)sb.range_row[warp] + lane); // row of run `lane`
   if (lane < nruns) job_round<TILE, true, STAGES>(p, sb, ctl, warp, r0, lane, njobs, first_is_head, gbase, prow);
 #pragma unroll 1
   for (uint32_t k = 32 + lane; k < nruns; k += 32) {
@@ -744,38 +772,60 @@ template <int TILE, int STAGES>
 __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
                                             uint32_t warp, uint32_t lane) {
   uint32_t s = 0, par = 0; // next tile to classify: stage, parity
-  const uint32_t base_addr = smem_u32_pinned(&ctl.base_ready[0]), done_addr = smem_u32_pinned(&ctl.p1done[0]);
   const uint32_t cols_addr = smem_u32_pinned(&ctl.cols[0]);
+  const uint32_t base_addr = smem_u32_pinned(&ctl.base_ready[0]);
+  const uint32_t done_addr = smem_u32_pinned(&ctl.p1done[0]);
   Watchdog wd;
 #ifdef NXS_TRACE_STATS
-  uint64_t st_idle = 0, st_busy = 0;
+  uint64_t st_idle = 0, st_busy = 0, st_idle_base = 0;
 #endif
   while (true) {
-    // Classify when the tile's first row index is known.  Until then an idle warp sleeps off the issue
-    // slots in a loop kept as short as possible (a barrier test, a nap): every instruction an idle warp
-    // issues is taken from a busy one.
+    // Wait for the tile's columns (the record pass needs neither the keys nor the job boundaries).  An idle
+    // warp sleeps off the issue slots in a loop kept as short as possible (a barrier test, a nap): every
+    // instruction an idle warp issues is taken from a busy one.
 #ifdef NXS_TRACE_STATS
     const uint64_t t_a = global_timer_ns();
 #endif
-    while (!__all_sync(0xffffffffu, mbar_test_wait_a(base_addr + 8u * s, par))) {
+    while (!__all_sync(0xffffffffu, mbar_test_wait_a(cols_addr + 8u * s, par))) {
       __nanosleep(NXS_IDLE_NS);
       wd.tick(p.counters + 2);
     }
 #ifdef NXS_TRACE_STATS
-    const uint64_t t_b = global_timer_ns();
+    uint64_t t_b = global_timer_ns();
     st_idle += t_b - t_a;
 #endif
-    // (the other columns landed long ago: they were issued with the keys, and marking and the look-back came between)
-    while (!__all_sync(0xffffffffu, mbar_test_wait_a(cols_addr + 8u * s, par))) wd.tick(p.counters + 2);
     wd.reset();
     StageBuf<TILE> &sb = stages[s];
     const int32_t t = sb.tile;
+    const bool full_tile = t >= 0 && p.n - (uint32_t)t * TILE >= (uint32_t)TILE;
     if (t >= 0) {
+      // (a ragged last tile is copied into the stage by the marker warps, not by the producer)
+      if (!full_tile) {
+        while (!__all_sync(0xffffffffu, mbar_test_wait(&ctl.marked[s], par))) wd.tick(p.counters + 2);
+        wd.reset();
+      }
+      // (1) the record pass
       if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_START, (uint32_t)t);
-      if (p.n - (uint32_t)t * TILE >= (uint32_t)TILE)
-        classify_range<TILE, true, STAGES>(p, sb, ctl, (uint32_t)t, warp, lane);
-      else
-        classify_range<TILE, false, STAGES>(p, sb, ctl, (uint32_t)t, warp, lane);
+      if (full_tile) record_pass<TILE, true, STAGES>(p, sb, ctl, (uint32_t)t, warp, lane);
+      else record_pass<TILE, false, STAGES>(p, sb, ctl, (uint32_t)t, warp, lane);
+      __syncwarp();
+      // (2) the job pass, once the look-back has delivered the index of the tile's first job row
+#ifdef NXS_TRACE_STATS
+      const uint64_t t_c = global_timer_ns();
+#endif
+      while (!__all_sync(0xffffffffu, mbar_test_wait_a(base_addr + 8u * s, par))) {
+        __nanosleep(NXS_IDLE_NS);
+        wd.tick(p.counters + 2);
+      }
+#ifdef NXS_TRACE_STATS
+      const uint64_t t_d = global_timer_ns();
+      st_idle += t_d - t_c;
+      st_idle_base += t_d - t_c;
+      t_b += t_d - t_c;
+#endif
+      wd.reset();
+      if (full_tile) job_pass<TILE, true, STAGES>(p, sb, ctl, (uint32_t)t, warp, lane);
+      else job_pass<TILE, false, STAGES>(p, sb, ctl, (uint32_t)t, warp, lane);
       if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_END, (uint32_t)t);
     }
     __syncwarp();
@@ -784,6 +834,7 @@ __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TI
     if (t < 0 && lane == 0) {
       NXS_TRACE_STAT(p, EV_W_IDLE, (uint32_t)(st_idle >> 4) | warp << 28);
       NXS_TRACE_STAT(p, EV_W_BUSY, (uint32_t)(st_busy >> 4) | warp << 28);
+      NXS_TRACE_STAT(p, EV_C_IDLE, (uint32_t)(st_idle_base >> 4) | warp << 28);
     }
 #endif
     if (lane == 0) mbar_arrive_a(done_addr + 8u * s);
@@ -856,7 +907,7 @@ __device__ __forceinline__ void summary_loop(const ClassifyParams &p, StageBuf<T
       const bool has_unres = mine && sb.range[lane].has_unres;
       const Summ unres = has_unres ? summ_unpack(sb.range[lane].unres) : summ_identity();
       const uint64_t ukey = has_unres ? sb.range[lane].unres_key : 0ull;
-      const uint32_t rowpos = mine ? sb.tile_base + sb.range_off[lane] : 0u;
+      const uint32_t rowpos = mine ? sb.range_row[lane] : 0u;
       const bool first_is_head = sb.first_is_head != 0;
       __syncwarp();
       if (lane == 0) mbar_arrive(&ctl.freeb[s]);
@@ -983,7 +1034,7 @@ __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&ctl.full[s], 2);
       mbar_init(&ctl.cols[s], 1);
-      mbar_init(&ctl.marked[s], kCounterWarps);
+      mbar_init(&ctl.marked[s], kMarkerWarps);
       mbar_init(&ctl.base_ready[s], 1);
       mbar_init(&ctl.p1done[s], kWorkerWarps);
       mbar_init(&ctl.freeb[s], 1);
@@ -1015,7 +1066,8 @@ __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__
   else if (warp == (uint32_t)kProducerWarp) {
     if (lane == 0) producer_loop<TILE, STAGES>(p, stages, ctl);
   } else if (warp == (uint32_t)kSummaryWarp) summary_loop<TILE, STAGES>(p, stages, ctl, lane);
-  else counter_loop<TILE, STAGES>(p, stages, ctl, warp - kCounterWarp0, lane);
+  else if (warp < (uint32_t)kMarkerWarp0) lookback_loop<TILE, STAGES>(p, stages, ctl, warp - kCounterWarp0, lane);
+  else marker_loop<TILE, STAGES>(p, stages, ctl, warp - kMarkerWarp0, lane);
 }
 
 #endif // __CUDACC__

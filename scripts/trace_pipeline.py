@@ -52,16 +52,17 @@ def main():
         cta, e, tile = int(w) >> 40, (int(w) >> 32) & 255, int(w) & 0xFFFFFFFF
         if e == 11:
             polls[(cta, tile)] = polls.get((cta, tile), 0) + 1
-        elif e in (14, 15):  # NXS_TRACE_STATS build: per-worker-warp idle / busy totals (ns / 16)
-            stats.setdefault(cta, {}).setdefault(tile >> 28, {})["idle" if e == 14 else "busy"] = (tile & 0xFFFFFFF) * 16
+        elif e in (14, 15, 18):  # NXS_TRACE_STATS build: per-worker-warp idle / busy totals (ns / 16)
+            stats.setdefault(cta, {}).setdefault(tile >> 28, {})[{14: "idle", 15: "busy", 18: "idle_base"}[e]] = (tile & 0xFFFFFFF) * 16
         elif e == 13:  # NXS_TRACE_STEPS build: end of 32-record step j of warp 0
             steps.setdefault((cta, tile & 0xFFFFFF), {})[tile >> 24] = int(t) - t0
         else:
             per.setdefault((cta, tile), {})[EV[e]] = int(t) - t0
     print(f"{cnt} events, span {(int(ev[:, 0].max()) - t0) / 1e3:.1f} us")
     for cta, ws in sorted(stats.items()):
-        print(f"--- CTA {cta}: worker warps, us waiting for a tile / us classifying: " +
-              "  ".join(f"w{w}: {v.get('idle', 0) / 1e3:.0f}/{v.get('busy', 0) / 1e3:.0f}" for w, v in sorted(ws.items())))
+        print(f"--- CTA {cta}: worker warps, us waiting (of which for the first row index) / us classifying: " +
+              "  ".join(f"w{w}: {v.get('idle', 0) / 1e3:.0f}({v.get('idle_base', 0) / 1e3:.0f})/{v.get('busy', 0) / 1e3:.0f}"
+                        for w, v in sorted(ws.items())))
     for cta in sorted({k[0] for k in per}):
         tiles = sorted(k[1] for k in per if k[0] == cta)
         print(f"--- CTA {cta}: {len(tiles)} tiles; claim in us from kernel start; durations in ns")
@@ -85,6 +86,13 @@ def main():
                 print(f"{tile:6d} {d['claim'] / 1e3:8.1f} | " + " ".join(f"{vals[k]:6d}" for k in cols))
         print(" median: " + "  ".join(f"{k}={int(np.median(v))}" for k, v in agg.items() if v))
         print(" mean:   " + "  ".join(f"{k}={int(np.mean(v))}" for k, v in agg.items() if v))
+        chain = np.array([per[(cta, t)]["lb_end"] - per[(cta, t)]["claim"] for t in tiles
+                          if "lb_end" in per[(cta, t)] and "claim" in per[(cta, t)]])
+        mk = np.array([per[(cta, t)]["count_end"] - per[(cta, t)]["claim"] for t in tiles
+                       if "count_end" in per[(cta, t)] and "claim" in per[(cta, t)]])
+        if len(chain):
+            q = lambda a: " / ".join(str(int(x)) for x in np.percentile(a, [50, 90, 99, 100]))  # noqa: E731
+            print(f" claim -> count published (ns, median / p90 / p99 / max): {q(mk)};  claim -> first row index known: {q(chain)}")
         st = [(per[k]["p1_start"], per[k].get("p1_end"), steps[k]) for k in steps if k[0] == cta and "p1_start" in per.get(k, {})]
         if st:
             nj = max(len(x[2]) for x in st)
