@@ -47,15 +47,10 @@ constexpr int kProducerWarp = kWorkerWarps;
 constexpr int kSummaryWarp = kWorkerWarps + 1;
 constexpr int kCounterWarp0 = kWorkerWarps + 2; // first of kCounterWarps counter warps
 #ifndef NXS_COUNTER_WARPS
-#define NXS_COUNTER_WARPS 2
+#define NXS_COUNTER_WARPS 4
 #endif
 constexpr int kCounterWarps = NXS_COUNTER_WARPS; // look-back warps: tile k of a CTA is looked up by warp k % kCounterWarps
-#ifndef NXS_MARKER_WARPS
-#define NXS_MARKER_WARPS 8
-#endif
-constexpr int kMarkerWarps = NXS_MARKER_WARPS; // each marks the job boundaries of its share of the worker ranges of every tile
-constexpr int kMarkerWarp0 = kCounterWarp0 + kCounterWarps;
-constexpr int kThreads = kWorkers + 64 + 32 * (kCounterWarps + kMarkerWarps);
+constexpr int kThreads = kWorkers + 64 + 32 * kCounterWarps;
 constexpr int kPendingSlots = 4;                // tiles whose carried-in summary is still being looked up
 constexpr uint64_t kWatchdogNs = 8000000000ull; // a stuck wait traps instead of hanging the GPU
 
@@ -114,10 +109,10 @@ template <int TILE> struct __align__(128) StageBuf {
   uint2 tailinfo[TILE / 32]; // .x bit b: record 32*chunk + b is the last of its job; .y: shared-memory address of the
                              //   list entry (see reason[]) of the first job that ends in the chunk
   RangeInfo range[kWorkerWarps];
-  uint32_t range_cnt[kWorkerWarps]; // jobs ending in each range                        (marker warps)
+  uint32_t range_cnt[kWorkerWarps]; // jobs ending in each range                        (workers, marking)
   uint32_t range_row[kWorkerWarps]; // index of the first job row of each range        (look-back warp)
   uint32_t tile_base;               // job rows before the tile                        (look-back warp)
-  uint32_t first_is_head;           // the tile's first record begins a job            (marker warp 0)
+  uint32_t first_is_head;           // the tile's first record begins a job            (worker 0, marking)
   int32_t tile;                     // tile id, -1 = end of work                       (producer)
   uint32_t total;                   // jobs ending in the tile                         (look-back warp)
 };
@@ -140,9 +135,9 @@ struct PendingTile {
 };
 
 template <int STAGES> struct Ctl {
-  uint64_t full[STAGES];       // the tile's keys landed    (producer -> marker warps)
+  uint64_t full[STAGES];       // the tile's keys landed    (producer -> workers, for the marking)
   uint64_t cols[STAGES];       // its other columns landed  (producer -> workers)
-  uint64_t marked[STAGES];     // job boundaries marked    (marker warps -> look-back warps, workers)
+  uint64_t marked[STAGES];     // job boundaries marked    (workers -> look-back warps)
   uint64_t base_ready[STAGES]; // first row index known    (look-back warp -> workers)
   uint64_t p1done[STAGES];     // rows written             (workers -> summary warp)
   uint64_t freeb[STAGES];      // stage reusable           (summary warp -> producer)
@@ -361,14 +356,12 @@ __device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<
   }
 }
 
-// ------------------------------------------------------- job boundaries (marker warps)
-// As soon as the keys of a tile have landed the marker warps mark it, each its share of the worker
-// ranges: per range (`warp` = the worker warp that owns it) the "last record of its job" bit mask of
-// every 32-record chunk, with the place in the job-end list where the chunk's first entry goes, and
-// the number of jobs that end in the range; range 0 also notes whether the tile's first record begins a
-// job.  They do nothing else and never wait for anything but the landing, so the tile's job count —
-// which every later tile of the grid waits for — is known a fixed, short time after the load.  A
-// ragged (last) tile is read from global memory here and copied into the stage for the other passes.
+// ------------------------------------------------------- job boundaries (workers, between their passes)
+// Every worker warp marks its own range of a tile as soon after the landing of the tile's keys as it
+// gets to look (see Marker below): the "last record of its job" bit mask of every 32-record chunk, with
+// the place in the job-end list where the chunk's first entry goes, and the number of jobs that end in
+// the range; warp 0 also notes whether the tile's first record begins a job.  A ragged (last) tile is
+// read from global memory here and copied into the stage for the other passes.
 template <int TILE, bool FULL>
 __device__ __forceinline__ void mark_range(const ClassifyParams &p, StageBuf<TILE> &sb, uint32_t tile, uint32_t warp,
                                            uint32_t lane) {
@@ -449,37 +442,50 @@ __device__ __forceinline__ bool count_lookback_poll(const ClassifyParams &p, Cou
   return false;
 }
 
-template <int TILE, int STAGES>
-__device__ __forceinline__ void marker_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
-                                            uint32_t which, uint32_t lane) {
-  static_assert(kWorkerWarps % kMarkerWarps == 0, "the worker ranges are split evenly among the marker warps");
-  constexpr uint32_t RPP = kWorkerWarps / kMarkerWarps;
-  Watchdog wd;
-  for (uint32_t k = 0;; ++k) {
-    const uint32_t s = k % STAGES;
-    while (!__all_sync(0xffffffffu, mbar_try_wait(&ctl.full[s], (k / STAGES) & 1u, 2000u))) wd.tick(p.counters + 2);
-    wd.reset();
-    StageBuf<TILE> &sb = stages[s];
-    const int32_t t = sb.tile;
-    if (t >= 0) {
-      if (which == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_COUNT_START, (uint32_t)t);
-      const bool full_tile = p.n - (uint32_t)t * TILE >= (uint32_t)TILE;
-#pragma unroll 1
-      for (uint32_t r = which * RPP; r < (which + 1) * RPP; ++r) {
-        if (full_tile) mark_range<TILE, true>(p, sb, (uint32_t)t, r, lane);
-        else mark_range<TILE, false>(p, sb, (uint32_t)t, r, lane);
-      }
-    }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&ctl.marked[s]);
-    if (t < 0) break;
+// The job count of a tile is what every later tile of the grid waits for (count look-back), so it
+// must be known a short, steady time after the tile has landed — whatever the workers are busy with.
+// Marking by warps of its own proved too slow for that: they get a fair share of the issue slots, which
+// the sixteen worker warps keep busy.  So the workers mark, out of turn: between two groups of the
+// record pass, between two rounds of the job pass and in every idle loop a worker warp tests the `full`
+// barrier of the next tile of the CTA it has not marked yet, and marks its range of it right away (a
+// few hundred nanoseconds).  Tiles are marked in claim order; a warp is never more than one use of a
+// stage behind (the stage's next use needs this warp's job pass), so the parity waits are safe.
+template <int TILE, int STAGES> struct Marker {
+  uint32_t km = 0;   // next tile of the CTA (in claim order) this warp has not marked yet
+  bool done = false; // the end marker has been passed on
+  uint32_t full_a, marked_a;
+  __device__ __forceinline__ bool pending(uint32_t lane) const {
+    (void)lane;
+    return !done && __all_sync(0xffffffffu, mbar_test_wait_a(full_a + 8u * (km % STAGES), (km / STAGES) & 1u));
   }
+};
+// (out of line, scalar arguments only: the caller's marker state stays in registers; returns true for the end marker)
+template <int TILE, int STAGES>
+__device__ __noinline__ bool mark_next(const ClassifyParams &p, StageBuf<TILE> *stages, uint32_t s, uint32_t marked_bar,
+                                       uint32_t warp, uint32_t lane) {
+  StageBuf<TILE> &sb = stages[s];
+  const int32_t t = sb.tile;
+  if (t >= 0) {
+    if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_COUNT_START, (uint32_t)t);
+    if (p.n - (uint32_t)t * TILE >= (uint32_t)TILE) mark_range<TILE, true>(p, sb, (uint32_t)t, warp, lane);
+    else mark_range<TILE, false>(p, sb, (uint32_t)t, warp, lane);
+  }
+  __syncwarp();
+  if (lane == 0) mbar_arrive_a(marked_bar);
+  return t < 0;
 }
+#define NXS_MARK_IF_LANDED()                                                                                      \
+  do {                                                                                                            \
+    if (mk.pending(lane)) {                                                                                       \
+      mk.done = mark_next<TILE, STAGES>(p, stages, mk.km % STAGES, mk.marked_a + 8u * (mk.km % STAGES), warp, lane); \
+      ++mk.km;                                                                                                    \
+    }                                                                                                             \
+  } while (0)
 
 // The look-back warps of a CTA take its tiles in turn: warp `which` OWNS the tiles k = which, which +
 // kCounterWarps, ... (k = order in which the CTA claimed them), so that several look-backs are in flight
 // per CTA: one look-back costs a few L2 round trips, more than the time a tile may take at full speed.
-// When the marker warps are done with an own tile, the warp adds up the ranges' job counts, publishes the
+// When the workers have marked an own tile, the warp adds up the ranges' job counts, publishes the
 // tile's job count — every later tile of every CTA waits for the counts — and then polls predecessor
 // counts for the index of the tile's first job row, which the workers need for the job pass only.
 // Each warp is an event loop: pass over the tiles of the CTA in order (publishing on the way), poll for
@@ -672,8 +678,9 @@ __device__ __forceinline__ void sts_u16(uint32_t addr, uint32_t v) {
 // onEvent: guards (:155,:161,:218) and the (kind, reason) switch arms, then superviseAction's order:
 // no checkpoint (:265) -> finished (:276) -> switch (:283).  All of it is table lookups.
 template <int TILE, bool FULL, int STAGES>
-__device__ __forceinline__ void record_pass(const ClassifyParams &p, StageBuf<TILE> &sb, const Ctl<STAGES> &ctl,
-                                            uint32_t tile, uint32_t warp, uint32_t lane) {
+__device__ __forceinline__ void record_pass(const ClassifyParams &p, StageBuf<TILE> *stages, StageBuf<TILE> &sb,
+                                            const Ctl<STAGES> &ctl, Marker<TILE, STAGES> &mk, uint32_t tile,
+                                            uint32_t warp, uint32_t lane) {
   static_assert(TILE % (kWorkerWarps * 32 * kRecordGroup) == 0, "a range is a whole number of record groups");
   constexpr uint32_t RANGE = TILE / kWorkerWarps; // records per warp
   constexpr uint32_t CPW = RANGE / 32;            // 32-record chunks per warp
@@ -688,6 +695,7 @@ __device__ __forceinline__ void record_pass(const ClassifyParams &p, StageBuf<TI
   uint32_t *pv = p.verdict + (size_t)start + r0 + lane;
 #pragma unroll 1
   for (uint32_t g = 0; g < CPW; g += kRecordGroup, pv += 32 * kRecordGroup) {
+    NXS_MARK_IF_LANDED();
     uint32_t vt[kRecordGroup], off[kRecordGroup];
     // loads and lookups of the whole group first: the stores below land on bytes read here
 #pragma unroll
@@ -717,8 +725,9 @@ __device__ __forceinline__ void record_pass(const ClassifyParams &p, StageBuf<TI
 
 // --------------------------------------------------------------------- job pass (a lane per run)
 template <int TILE, bool FULL, int STAGES>
-__device__ __forceinline__ void job_pass(const ClassifyParams &p, StageBuf<TILE> &sb, const Ctl<STAGES> &ctl,
-                                         uint32_t tile, uint32_t warp, uint32_t lane) {
+__device__ __forceinline__ void job_pass(const ClassifyParams &p, StageBuf<TILE> *stages, StageBuf<TILE> &sb,
+                                         const Ctl<STAGES> &ctl, Marker<TILE, STAGES> &mk, uint32_t tile, uint32_t warp,
+                                         uint32_t lane) {
   constexpr uint32_t RANGE = TILE / kWorkerWarps;
   const uint32_t start = tile * TILE;
   const uint32_t cnt = FULL ? (uint32_t)TILE : p.n - start;
@@ -759,9 +768,10 @@ __device__ __forceinline__ void job_pass(const ClassifyParams &p, StageBuf<TILE>
   nxs_job_row *prow = p.rows + ((size_t)sb.range_row[warp] + lane); // row of run `lane`
   if (lane < nruns) job_round<TILE, true, STAGES>(p, sb, ctl, warp, r0, lane, njobs, first_is_head, gbase, prow);
 #pragma unroll 1
-  for (uint32_t k = 32 + lane; k < nruns; k += 32) {
+  for (uint32_t kb = 32; kb < nruns; kb += 32) {
+    NXS_MARK_IF_LANDED();
     prow += 32;
-    job_round<TILE, false, STAGES>(p, sb, ctl, warp, r0, k, njobs, first_is_head, gbase, prow);
+    if (kb + lane < nruns) job_round<TILE, false, STAGES>(p, sb, ctl, warp, r0, kb + lane, njobs, first_is_head, gbase, prow);
   }
   // the stage's columns were written here through the generic proxy; the next tile lands in them through the async proxy
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -771,22 +781,26 @@ __device__ __forceinline__ void job_pass(const ClassifyParams &p, StageBuf<TILE>
 template <int TILE, int STAGES>
 __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
                                             uint32_t warp, uint32_t lane) {
-  uint32_t s = 0, par = 0; // next tile to classify: stage, parity
+  uint32_t s = 0, par = 0, k = 0; // next tile to classify: stage, parity, index in the CTA's claim order
   const uint32_t cols_addr = smem_u32_pinned(&ctl.cols[0]);
   const uint32_t base_addr = smem_u32_pinned(&ctl.base_ready[0]);
   const uint32_t done_addr = smem_u32_pinned(&ctl.p1done[0]);
+  Marker<TILE, STAGES> mk;
+  mk.full_a = smem_u32_pinned(&ctl.full[0]);
+  mk.marked_a = smem_u32_pinned(&ctl.marked[0]);
   Watchdog wd;
 #ifdef NXS_TRACE_STATS
   uint64_t st_idle = 0, st_busy = 0, st_idle_base = 0;
 #endif
   while (true) {
     // Wait for the tile's columns (the record pass needs neither the keys nor the job boundaries).  An idle
-    // warp sleeps off the issue slots in a loop kept as short as possible (a barrier test, a nap): every
+    // warp sleeps off the issue slots in a loop kept as short as possible (barrier tests, a nap): every
     // instruction an idle warp issues is taken from a busy one.
 #ifdef NXS_TRACE_STATS
     const uint64_t t_a = global_timer_ns();
 #endif
     while (!__all_sync(0xffffffffu, mbar_test_wait_a(cols_addr + 8u * s, par))) {
+      NXS_MARK_IF_LANDED();
       __nanosleep(NXS_IDLE_NS);
       wd.tick(p.counters + 2);
     }
@@ -798,22 +812,27 @@ __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TI
     StageBuf<TILE> &sb = stages[s];
     const int32_t t = sb.tile;
     const bool full_tile = t >= 0 && p.n - (uint32_t)t * TILE >= (uint32_t)TILE;
-    if (t >= 0) {
-      // (a ragged last tile is copied into the stage by the marker warps, not by the producer)
-      if (!full_tile) {
-        while (!__all_sync(0xffffffffu, mbar_test_wait(&ctl.marked[s], par))) wd.tick(p.counters + 2);
-        wd.reset();
+    // A ragged last tile is copied into the stage by the marking (not by the producer), and the end
+    // marker must be passed on to the look-back warps before this warp leaves: mark up to this tile first.
+    if (!full_tile) {
+      while (mk.km <= k && !mk.done) {
+        NXS_MARK_IF_LANDED();
+        wd.tick(p.counters + 2);
       }
+      wd.reset();
+    }
+    if (t >= 0) {
       // (1) the record pass
       if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_START, (uint32_t)t);
-      if (full_tile) record_pass<TILE, true, STAGES>(p, sb, ctl, (uint32_t)t, warp, lane);
-      else record_pass<TILE, false, STAGES>(p, sb, ctl, (uint32_t)t, warp, lane);
+      if (full_tile) record_pass<TILE, true, STAGES>(p, stages, sb, ctl, mk, (uint32_t)t, warp, lane);
+      else record_pass<TILE, false, STAGES>(p, stages, sb, ctl, mk, (uint32_t)t, warp, lane);
       __syncwarp();
       // (2) the job pass, once the look-back has delivered the index of the tile's first job row
 #ifdef NXS_TRACE_STATS
       const uint64_t t_c = global_timer_ns();
 #endif
       while (!__all_sync(0xffffffffu, mbar_test_wait_a(base_addr + 8u * s, par))) {
+        NXS_MARK_IF_LANDED();
         __nanosleep(NXS_IDLE_NS);
         wd.tick(p.counters + 2);
       }
@@ -824,8 +843,8 @@ __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TI
       t_b += t_d - t_c;
 #endif
       wd.reset();
-      if (full_tile) job_pass<TILE, true, STAGES>(p, sb, ctl, (uint32_t)t, warp, lane);
-      else job_pass<TILE, false, STAGES>(p, sb, ctl, (uint32_t)t, warp, lane);
+      if (full_tile) job_pass<TILE, true, STAGES>(p, stages, sb, ctl, mk, (uint32_t)t, warp, lane);
+      else job_pass<TILE, false, STAGES>(p, stages, sb, ctl, mk, (uint32_t)t, warp, lane);
       if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_END, (uint32_t)t);
     }
     __syncwarp();
@@ -839,6 +858,7 @@ __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TI
 #endif
     if (lane == 0) mbar_arrive_a(done_addr + 8u * s);
     if (t < 0) break;
+    ++k;
     if (++s == STAGES) s = 0, par ^= 1u;
   }
 }
@@ -1034,7 +1054,7 @@ __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&ctl.full[s], 2);
       mbar_init(&ctl.cols[s], 1);
-      mbar_init(&ctl.marked[s], kMarkerWarps);
+      mbar_init(&ctl.marked[s], kWorkerWarps);
       mbar_init(&ctl.base_ready[s], 1);
       mbar_init(&ctl.p1done[s], kWorkerWarps);
       mbar_init(&ctl.freeb[s], 1);
@@ -1066,8 +1086,7 @@ __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__
   else if (warp == (uint32_t)kProducerWarp) {
     if (lane == 0) producer_loop<TILE, STAGES>(p, stages, ctl);
   } else if (warp == (uint32_t)kSummaryWarp) summary_loop<TILE, STAGES>(p, stages, ctl, lane);
-  else if (warp < (uint32_t)kMarkerWarp0) lookback_loop<TILE, STAGES>(p, stages, ctl, warp - kCounterWarp0, lane);
-  else marker_loop<TILE, STAGES>(p, stages, ctl, warp - kMarkerWarp0, lane);
+  else lookback_loop<TILE, STAGES>(p, stages, ctl, warp - kCounterWarp0, lane);
 }
 
 #endif // __CUDACC__
