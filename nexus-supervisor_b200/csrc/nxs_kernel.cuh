@@ -5,33 +5,38 @@
 // the records of each job into one row.  Each CTA is a warp-specialised pipeline
 // over a ring of shared-memory stages, driven by mbarriers only:
 //
-//   producer warp   claims a tile id from a global counter when a stage is about to be free and
-//                   streams the five input columns of the tile into the stage with 1-D bulk async
-//                   copies (TMA engine, SASS UBLKCP); the keys land on their own barrier
-//   worker warps    each warp owns a contiguous range of the tile and makes three passes over it.
-//                   Marking, as soon as the keys have landed: adjacent keys compared, the "last
-//                   record of a job" bit masks and the range's job count left in the stage.
+//   producer warp   claims tile ids from a global counter ONE TILE AHEAD of the ring (the id of the
+//                   tile that will use the next stage to come free is already known) and streams the
+//                   five input columns of a tile into its stage with 1-D bulk async copies (TMA
+//                   engine, SASS UBLKCP)
+//   marker warps    as soon as a tile id is claimed — a tile time before the tile's stage is even
+//                   free — they read the tile's job keys straight from global memory (they reach
+//                   shared memory a little later through L2), compare adjacent keys and leave the
+//                   "last record of a job" bit masks and the jobs-per-range counts in the tile's
+//                   slot of a small ring of tile descriptions (TileMeta)
+//   look-back warps (they take the tiles in turn) add up the ranges' counts, publish the tile's JOB
+//                   COUNT, poll predecessor tiles (decoupled look-back on counts only) for the
+//                   index of the tile's first job row.  Marking and look-back run a tile ahead of
+//                   the ring, so by the time a tile has landed its row positions are known: no
+//                   stage ever waits for them
+//   worker warps    each warp owns a contiguous range of the tile and makes two passes over it.
 //                   Record pass, 32 records at a time, lane per record: table lookups -> packed
 //                   verdict -> global; four warp ballots -> one row of bit masks per 32 records, kept
 //                   in the stage in place of the columns just consumed, as are the switch arm of
 //                   every record and the list of the positions where jobs end.
-//                   Job pass, lane per JOB, once the index of the tile's first job row is known: a
-//                   lane cuts its job's bits out of the mask rows with funnel shifts, folds them with
-//                   a dozen bit operations and stores the 16-byte job row at its final position —
-//                   every lane does useful work, whatever the share of records that end a job
-//   look-back warps (they take the tiles in turn) when a tile is marked: add up the ranges' job
-//                   counts, publish the tile's JOB COUNT, poll predecessor tiles (decoupled look-back
-//                   on counts only) for the index of the tile's first job row — all of it while the
-//                   workers run the record pass
+//                   Job pass, lane per JOB: a lane cuts its job's bits out of the mask rows with
+//                   funnel shifts, folds them with a dozen bit operations and stores the 16-byte
+//                   job row at its final position — every lane does useful work, whatever the share
+//                   of records that end a job
 //   summary warp    after the workers: frees the stage, publishes the summary of
 //                   the job left open at the tile's end, and writes the few rows
 //                   the workers could not close — jobs that began before a
 //                   warp's range or before the tile (the latter after a second,
 //                   off-the-critical-path look-back on summaries)
 //
-// Splitting the look-back in two keeps the stage's residency short: the count is
-// known as soon as the keys have landed and been compared, so the count look-back
-// runs beside the record pass and no stage waits for another CTA's classification.
+// Splitting the look-back in two keeps the stage's residency short: the count depends on the keys
+// alone, so it is published — and the row positions looked up — while the tile is still on its way,
+// and no stage waits for another CTA's classification.
 // Scratch: TileDesc[n_tiles] (16 B each) + 3 counters.
 #pragma once
 #include "nxs_device.cuh"
@@ -47,10 +52,15 @@ constexpr int kProducerWarp = kWorkerWarps;
 constexpr int kSummaryWarp = kWorkerWarps + 1;
 constexpr int kCounterWarp0 = kWorkerWarps + 2; // first of kCounterWarps counter warps
 #ifndef NXS_COUNTER_WARPS
-#define NXS_COUNTER_WARPS 4
+#define NXS_COUNTER_WARPS 2
 #endif
 constexpr int kCounterWarps = NXS_COUNTER_WARPS; // look-back warps: tile k of a CTA is looked up by warp k % kCounterWarps
-constexpr int kThreads = kWorkers + 64 + 32 * kCounterWarps;
+#ifndef NXS_MARKER_WARPS
+#define NXS_MARKER_WARPS 8
+#endif
+constexpr int kMarkerWarps = NXS_MARKER_WARPS; // each marks the job boundaries of its share of the worker ranges of every tile
+constexpr int kMarkerWarp0 = kCounterWarp0 + kCounterWarps;
+constexpr int kThreads = kWorkers + 64 + 32 * (kCounterWarps + kMarkerWarps);
 constexpr int kPendingSlots = 4;                // tiles whose carried-in summary is still being looked up
 constexpr uint64_t kWatchdogNs = 8000000000ull; // a stuck wait traps instead of hanging the GPU
 
@@ -77,9 +87,11 @@ constexpr uint64_t kWatchdogNs = 8000000000ull; // a stuck wait traps instead of
 #endif
 constexpr int kStageBudgetBytes = NXS_SMEM_BUDGET_KB * 1024;
 template <int TILE> struct StagesFor {
-  static constexpr int per_stage = TILE * 13 + TILE / 4 + 256 + 48 * NXS_WORKERS; // ~ sizeof(StageBuf<TILE>)
-  static constexpr int fit = kStageBudgetBytes / per_stage;
+  static constexpr int per_stage = TILE * 13 + 256 + 40 * NXS_WORKERS; // ~ sizeof(StageBuf<TILE>)
+  static constexpr int per_meta = TILE / 4 + 8 * NXS_WORKERS + 64;     // ~ sizeof(TileMeta<TILE>); one slot more than stages
+  static constexpr int fit = (kStageBudgetBytes - per_meta) / (per_stage + per_meta);
   static constexpr int value = fit < 2 ? 2 : fit > NXS_MAX_STAGES ? NXS_MAX_STAGES : fit;
+  static constexpr int metas = value + 1; // the tile claimed ahead of the ring has its description too
 };
 
 // What a worker warp leaves behind for its range of the tile.
@@ -106,15 +118,21 @@ template <int TILE> struct __align__(128) StageBuf {
   uint8_t kind[TILE];
   alignas(16) uint8_t flags[TILE];
   alignas(16) uint8_t stage[TILE];
-  uint2 tailinfo[TILE / 32]; // .x bit b: record 32*chunk + b is the last of its job; .y: shared-memory address of the
-                             //   list entry (see reason[]) of the first job that ends in the chunk
   RangeInfo range[kWorkerWarps];
-  uint32_t range_cnt[kWorkerWarps]; // jobs ending in each range                        (workers, marking)
+};
+
+// What is known about a tile before (and independently of) its records: written by the producer (the
+// id), the marker warps and the look-back warp while the tile is still on its way.  A ring of
+// STAGES + 1 slots: the tile claimed ahead of the ring has one too.
+template <int TILE> struct __align__(16) TileMeta {
+  uint2 tailinfo[TILE / 32]; // .x bit b: record 32*chunk + b is the last of its job; .y: shared-memory address of the
+                             //   list entry (see StageBuf::reason) of the first job that ends in the chunk
+  uint32_t range_cnt[kWorkerWarps]; // jobs ending in each worker range                (marker warps)
   uint32_t range_row[kWorkerWarps]; // index of the first job row of each range        (look-back warp)
-  uint32_t tile_base;               // job rows before the tile                        (look-back warp)
-  uint32_t first_is_head;           // the tile's first record begins a job            (worker 0, marking)
-  int32_t tile;                     // tile id, -1 = end of work                       (producer)
+  uint32_t first_is_head;           // the tile's first record begins a job            (marker warp 0)
   uint32_t total;                   // jobs ending in the tile                         (look-back warp)
+  int32_t tile;                     // tile id, -1 = end of work                       (producer)
+  uint32_t pad;
 };
 
 // Verdict table entry = packed verdict of the record plus the fold bits above it.
@@ -135,12 +153,15 @@ struct PendingTile {
 };
 
 template <int STAGES> struct Ctl {
-  uint64_t full[STAGES];       // the tile's keys landed    (producer -> workers, for the marking)
-  uint64_t cols[STAGES];       // its other columns landed  (producer -> workers)
-  uint64_t marked[STAGES];     // job boundaries marked    (workers -> look-back warps)
-  uint64_t base_ready[STAGES]; // first row index known    (look-back warp -> workers)
-  uint64_t p1done[STAGES];     // rows written             (workers -> summary warp)
-  uint64_t freeb[STAGES];      // stage reusable           (summary warp -> producer)
+  // per stage of the ring
+  uint64_t full[STAGES];   // the tile's keys landed        (producer -> workers, job pass)
+  uint64_t cols[STAGES];   // its other columns landed      (producer -> workers, record pass)
+  uint64_t p1done[STAGES]; // rows written                  (workers -> summary warp, producer)
+  uint64_t freeb[STAGES];  // stage reusable                (summary warp -> producer)
+  // per slot of the ring of tile descriptions (STAGES + 1 slots: they run a tile ahead of the stages)
+  uint64_t claimed[STAGES + 1];    // tile id known           (producer -> everybody)
+  uint64_t marked[STAGES + 1];     // job boundaries marked   (marker warps -> look-back warps, workers)
+  uint64_t base_ready[STAGES + 1]; // first row index known   (look-back warp -> workers)
   PendingTile pending[kPendingSlots];
   // Tables of the classification pass.  Entries are pre-scaled to byte offsets so that an address is
   // one instruction: vt entry of a record = vt + lut[..] + lut2[..].
@@ -203,7 +224,8 @@ struct ClassifyParams {
 };
 
 template <int TILE> constexpr size_t classify_smem_bytes() {
-  return sizeof(StageBuf<TILE>) * StagesFor<TILE>::value; // dynamic part: the ring (Ctl is a static __shared__ object)
+  // dynamic part: the ring of stages and the ring of tile descriptions (Ctl is a static __shared__ object)
+  return sizeof(StageBuf<TILE>) * StagesFor<TILE>::value + sizeof(TileMeta<TILE>) * StagesFor<TILE>::metas;
 }
 
 #if defined(__CUDACC__)
@@ -294,59 +316,57 @@ __device__ __forceinline__ Summ shfl_summ(Summ s, int src) {
 }
 
 // --------------------------------------------------------------------- producer
+// Tile k of the CTA (k = 0, 1, ... in claim order) uses stage k % STAGES of the ring and slot
+// k % (STAGES + 1) of the tile descriptions.  Its id is claimed one tile early: when tile k - 1 is
+// sent on its way.  Every CTA does the same, so the ids are still claimed in the order in which
+// the tiles will be loaded (which is what keeps the look-backs short), but the marker and look-back
+// warps learn the id a whole tile time before the stage is free, and have the tile's job count and
+// first row index ready when it lands.  A CTA never holds more than one id without a stage.
 template <int TILE, int STAGES>
-__device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl) {
+__device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<TILE> *stages, TileMeta<TILE> *metas,
+                                              Ctl<STAGES> &ctl) {
+  constexpr uint32_t METAS = STAGES + 1;
   Watchdog wd;
-  // the first tiles of the CTA (one per stage when there is enough work) are claimed in one go
-  const uint32_t per_cta = (p.n_tiles + gridDim.x - 1) / gridDim.x;
-  const uint32_t n_first = per_cta < (uint32_t)STAGES ? per_cta : (uint32_t)STAGES;
-  const uint32_t first = atomicAdd(p.counters, n_first);
-  for (uint32_t k = 0;; ++k) {
+  auto publish = [&](uint32_t k, uint32_t id) { // the id of tile k of the CTA: into its slot, and tell everybody
+    metas[k % METAS].tile = id < p.n_tiles ? (int32_t)id : -1;
+    mbar_arrive(&ctl.claimed[k % METAS]);
+    // the tile's keys on their way into L2 at once: the marker warps read them next, the ring a tile time later
+    if (id < p.n_tiles && p.n - id * TILE >= (uint32_t)TILE) bulk_prefetch_l2(p.key + (size_t)id * TILE, 8u * TILE);
+    if (id < p.n_tiles) NXS_TRACE_EVENT(p, EV_CLAIM, id);
+  };
+  uint32_t id = atomicAdd(p.counters, 1u);
+  publish(0, id);
+  for (uint32_t k = 0; id < p.n_tiles; ++k) {
     const uint32_t s = k % STAGES, use = k / STAGES;
-    // A tile id is claimed only when its stage is about to be free: every later tile of the grid waits
-    // (in its look-back) for the count of this one, so an id must not be held while the ring is full.
-    // The claim is issued when the workers are done with the stage's previous tile, and its round trip
-    // overlaps the summary warp's last reads of the stage.
-    if (use > 0) {
+    if (use > 0) { // the workers and the summary warp are done with the stage's previous tile (tile k - STAGES)
       while (!mbar_try_wait(&ctl.p1done[s], (use - 1) & 1u, 20000u)) {
         aux_nap<NXS_PRODUCER_NS>();
         wd.tick(p.counters + 2);
       }
-    }
-    const uint32_t id = k < n_first ? first + k : atomicAdd(p.counters, 1u);
-    if (use > 0) {
       while (!mbar_try_wait(&ctl.freeb[s], (use - 1) & 1u, 20000u)) wd.tick(p.counters + 2);
       wd.reset();
     }
     StageBuf<TILE> &sb = stages[s];
-    uint64_t *bar = &ctl.full[s];
-    if (id >= p.n_tiles) {
-      sb.tile = -1;
-      mbar_arrive_n(bar, 2);
-      mbar_arrive(&ctl.cols[s]);
-      break;
-    }
-    NXS_TRACE_EVENT(p, EV_CLAIM, id);
-    sb.tile = (int32_t)id;
     const uint32_t start = id * TILE;
     if (p.n - start >= (uint32_t)TILE) {
-      // the keys first, on their own barrier: marking the job boundaries needs nothing else
-      mbar_arrive_expect_tx(bar, 8u * TILE);
-      bulk_g2s(&sb.keyx[2], p.key + start, 8u * TILE, bar);
-      if (start > 0) cp_async_8(&sb.keyx[1], p.key + start - 1);
-      if (start + TILE < p.n) cp_async_8(&sb.keyx[2 + TILE], p.key + start + TILE);
-      mbar_arrive_after_cp_async(bar);
       uint64_t *cbar = &ctl.cols[s];
       mbar_arrive_expect_tx(cbar, 5u * TILE);
       bulk_g2s(sb.reason, p.reason + start, 2u * TILE, cbar);
       bulk_g2s(sb.kind, p.kind + start, TILE, cbar);
       bulk_g2s(sb.flags, p.flags + start, TILE, cbar);
       bulk_g2s(sb.stage, p.stage + start, TILE, cbar);
+      // (the keys are needed last: for the rows, in the job pass)
+      uint64_t *bar = &ctl.full[s];
+      mbar_arrive_expect_tx(bar, 8u * TILE);
+      bulk_g2s(&sb.keyx[2], p.key + start, 8u * TILE, bar);
       NXS_TRACE_EVENT(p, EV_ISSUED, id);
-    } else {
-      mbar_arrive_n(bar, 2); // ragged last tile: the counter warps load it themselves
+    } else { // ragged last tile: the workers copy their ranges themselves
+      mbar_arrive(&ctl.full[s]);
       mbar_arrive(&ctl.cols[s]);
     }
+    // The next id.  Its slot was last used by tile k - STAGES, which the summary warp has just let go of.
+    id = atomicAdd(p.counters, 1u);
+    publish(k + 1, id);
   }
   // leave the counters zero for the next launch: the last CTA to stop claiming resets them
   __threadfence();
@@ -356,52 +376,69 @@ __device__ __forceinline__ void producer_loop(const ClassifyParams &p, StageBuf<
   }
 }
 
-// ------------------------------------------------------- job boundaries (workers, between their passes)
-// Every worker warp marks its own range of a tile as soon after the landing of the tile's keys as it
-// gets to look (see Marker below): the "last record of its job" bit mask of every 32-record chunk, with
-// the place in the job-end list where the chunk's first entry goes, and the number of jobs that end in
-// the range; warp 0 also notes whether the tile's first record begins a job.  A ragged (last) tile is
-// read from global memory here and copied into the stage for the other passes.
-template <int TILE, bool FULL>
-__device__ __forceinline__ void mark_range(const ClassifyParams &p, StageBuf<TILE> &sb, uint32_t tile, uint32_t warp,
-                                           uint32_t lane) {
+// ------------------------------------------------------- job boundaries (marker warps)
+// As soon as a tile id is claimed the marker warps mark the tile, each its share of the worker ranges:
+// per range (`range` = the worker warp that owns it) the "last record of its job" bit mask of every
+// 32-record chunk, with the place in the job-end list where the chunk's first entry goes, and the
+// number of jobs that end in the range; range 0 also notes whether the tile's first record begins a
+// job.  The keys are read straight from global memory — the tile itself is loaded later — so nothing
+// here waits for the ring: the tile's job count, which every later tile of the grid waits for, is
+// known long before the tile's stage is free.  (The same bytes reach shared memory through L2 a few
+// microseconds later; HBM delivers them once.)
+template <int TILE>
+__device__ __forceinline__ void mark_range(const ClassifyParams &p, TileMeta<TILE> &tm, uint32_t ends_a, uint32_t tile,
+                                           uint32_t range, uint32_t lane) {
   constexpr uint32_t RANGE = TILE / kWorkerWarps, CPW = RANGE / 32;
-  const uint32_t start = tile * TILE, r0 = warp * RANGE;
-  const uint32_t ends_a = smem_u32(sb.reason + r0); // job-end list of the range (see StageBuf)
+  const uint32_t g0 = tile * TILE + range * RANGE; // first record of the range
+  const uint64_t *const key = p.key + g0 + lane;
   uint32_t jobs = 0;
-  if (FULL) {
-    const bool last_tile = start + TILE == p.n;
+  if (g0 + RANGE < p.n) { // the range and the record behind it exist
 #pragma unroll
     for (uint32_t j = 0; j < CPW; ++j) {
-      const uint32_t i = r0 + j * 32 + lane;
-      bool tail = sb.keyx[2 + i] != sb.keyx[3 + i];
-      if (last_tile && i == TILE - 1) tail = true;
+      const bool tail = __ldg(key + j * 32) != __ldg(key + j * 32 + 1);
       const uint32_t T = __ballot_sync(0xffffffffu, tail);
-      if (lane == 0) sb.tailinfo[r0 / 32 + j] = make_uint2(T, ends_a + 2u * jobs);
+      if (lane == 0) tm.tailinfo[range * CPW + j] = make_uint2(T, ends_a + 2u * jobs);
       jobs += __popc(T);
     }
-    if (warp == 0 && lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(sb.keyx[2] != sb.keyx[1]);
-  } else { // ragged last tile (once per launch)
-    const uint32_t cnt = p.n - start;
+  } else { // the end of the batch falls in (or right behind) this range
     for (uint32_t j = 0; j < CPW; ++j) {
-      const uint32_t i = r0 + j * 32 + lane;
+      const uint32_t g = g0 + j * 32 + lane;
       bool tail = false;
-      if (i < cnt) {
-        const uint64_t key = p.key[start + i];
-        tail = (i == cnt - 1) || key != p.key[start + i + 1];
-        sb.keyx[2 + i] = key;
-        sb.reason[i] = p.reason[start + i];
-        sb.kind[i] = p.kind[start + i];
-        sb.flags[i] = p.flags[start + i];
-        sb.stage[i] = p.stage[start + i];
-      }
+      if (g < p.n) tail = g + 1 == p.n || p.key[g] != p.key[g + 1];
       const uint32_t T = __ballot_sync(0xffffffffu, tail);
-      if (lane == 0) sb.tailinfo[r0 / 32 + j] = make_uint2(T, ends_a + 2u * jobs);
+      if (lane == 0) tm.tailinfo[range * CPW + j] = make_uint2(T, ends_a + 2u * jobs);
       jobs += __popc(T);
     }
-    if (warp == 0 && lane == 0) sb.first_is_head = (start == 0) ? 1u : (uint32_t)(p.key[start] != p.key[start - 1]);
   }
-  if (lane == 0) sb.range_cnt[warp] = jobs;
+  if (lane == 0) {
+    tm.range_cnt[range] = jobs;
+    if (range == 0) tm.first_is_head = g0 == 0 ? 1u : (uint32_t)(p.key[g0] != p.key[g0 - 1]);
+  }
+}
+
+template <int TILE, int STAGES>
+__device__ __forceinline__ void marker_loop(const ClassifyParams &p, StageBuf<TILE> *stages, TileMeta<TILE> *metas,
+                                            Ctl<STAGES> &ctl, uint32_t which, uint32_t lane) {
+  static_assert(kWorkerWarps % kMarkerWarps == 0, "the worker ranges are split evenly among the marker warps");
+  constexpr uint32_t METAS = STAGES + 1, RPP = kWorkerWarps / kMarkerWarps, RANGE = TILE / kWorkerWarps;
+  Watchdog wd;
+  for (uint32_t k = 0;; ++k) {
+    const uint32_t m = k % METAS;
+    while (!__all_sync(0xffffffffu, mbar_try_wait(&ctl.claimed[m], (k / METAS) & 1u, 2000u))) wd.tick(p.counters + 2);
+    wd.reset();
+    TileMeta<TILE> &tm = metas[m];
+    const int32_t t = tm.tile;
+    if (t >= 0) {
+      if (which == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_COUNT_START, (uint32_t)t);
+      StageBuf<TILE> &sb = stages[k % STAGES]; // (only its address is used: where the job-end lists will live)
+#pragma unroll 1
+      for (uint32_t r = which * RPP; r < (which + 1) * RPP; ++r)
+        mark_range<TILE>(p, tm, smem_u32(sb.reason + r * RANGE), (uint32_t)t, r, lane);
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&ctl.marked[m]);
+    if (t < 0) break;
+  }
 }
 
 // ----------------------------------------------------------------- counter warp
@@ -442,59 +479,20 @@ __device__ __forceinline__ bool count_lookback_poll(const ClassifyParams &p, Cou
   return false;
 }
 
-// The job count of a tile is what every later tile of the grid waits for (count look-back), so it
-// must be known a short, steady time after the tile has landed — whatever the workers are busy with.
-// Marking by warps of its own proved too slow for that: they get a fair share of the issue slots, which
-// the sixteen worker warps keep busy.  So the workers mark, out of turn: between two groups of the
-// record pass, between two rounds of the job pass and in every idle loop a worker warp tests the `full`
-// barrier of the next tile of the CTA it has not marked yet, and marks its range of it right away (a
-// few hundred nanoseconds).  Tiles are marked in claim order; a warp is never more than one use of a
-// stage behind (the stage's next use needs this warp's job pass), so the parity waits are safe.
-template <int TILE, int STAGES> struct Marker {
-  uint32_t km = 0;   // next tile of the CTA (in claim order) this warp has not marked yet
-  bool done = false; // the end marker has been passed on
-  uint32_t full_a, marked_a;
-  __device__ __forceinline__ bool pending(uint32_t lane) const {
-    (void)lane;
-    return !done && __all_sync(0xffffffffu, mbar_test_wait_a(full_a + 8u * (km % STAGES), (km / STAGES) & 1u));
-  }
-};
-// (out of line, scalar arguments only: the caller's marker state stays in registers; returns true for the end marker)
-template <int TILE, int STAGES>
-__device__ __noinline__ bool mark_next(const ClassifyParams &p, StageBuf<TILE> *stages, uint32_t s, uint32_t marked_bar,
-                                       uint32_t warp, uint32_t lane) {
-  StageBuf<TILE> &sb = stages[s];
-  const int32_t t = sb.tile;
-  if (t >= 0) {
-    if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_COUNT_START, (uint32_t)t);
-    if (p.n - (uint32_t)t * TILE >= (uint32_t)TILE) mark_range<TILE, true>(p, sb, (uint32_t)t, warp, lane);
-    else mark_range<TILE, false>(p, sb, (uint32_t)t, warp, lane);
-  }
-  __syncwarp();
-  if (lane == 0) mbar_arrive_a(marked_bar);
-  return t < 0;
-}
-#define NXS_MARK_IF_LANDED()                                                                                      \
-  do {                                                                                                            \
-    if (mk.pending(lane)) {                                                                                       \
-      mk.done = mark_next<TILE, STAGES>(p, stages, mk.km % STAGES, mk.marked_a + 8u * (mk.km % STAGES), warp, lane); \
-      ++mk.km;                                                                                                    \
-    }                                                                                                             \
-  } while (0)
-
 // The look-back warps of a CTA take its tiles in turn: warp `which` OWNS the tiles k = which, which +
-// kCounterWarps, ... (k = order in which the CTA claimed them), so that several look-backs are in flight
-// per CTA: one look-back costs a few L2 round trips, more than the time a tile may take at full speed.
-// When the workers have marked an own tile, the warp adds up the ranges' job counts, publishes the
-// tile's job count — every later tile of every CTA waits for the counts — and then polls predecessor
-// counts for the index of the tile's first job row, which the workers need for the job pass only.
-// Each warp is an event loop: pass over the tiles of the CTA in order (publishing on the way), poll for
-// the oldest own tile in between.  Every warp watches every use of every `marked` barrier in order; a
-// stage cannot be marked twice more while a look-back for it is pending (its next use needs the stage
-// back, which needs this look-back), so no parity wait can mistake a phase for the one two before.
+// kCounterWarps, ... (k = order in which the CTA claimed them), so that several look-backs can be in
+// flight per CTA.  When the marker warps are done with an own tile, the warp adds up the ranges' job
+// counts, publishes the tile's job count — every later tile of every CTA waits for the counts — and
+// then polls predecessor counts for the index of the tile's first job row, which the workers need for
+// the job pass.  Each warp is an event loop: pass over the tiles of the CTA in order (publishing on
+// the way), poll for the oldest own tile in between.  Every warp watches every use of every `marked`
+// barrier in order; a slot cannot be marked twice more while a look-back for it is pending (its next
+// use needs the slot's tile classified, which needs this look-back), so no parity wait can mistake a
+// phase for the one two before.
 template <int TILE, int STAGES>
-__device__ __forceinline__ void lookback_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
+__device__ __forceinline__ void lookback_loop(const ClassifyParams &p, TileMeta<TILE> *metas, Ctl<STAGES> &ctl,
                                               uint32_t which, uint32_t lane) {
+  constexpr uint32_t METAS = STAGES + 1;
   uint32_t km = 0;              // next tile of the CTA whose marking to await (all of them, in order)
   uint32_t kl = which;          // next own tile to look back for
   uint32_t k_end = 0xFFFFFFFFu; // index of the end marker, once seen
@@ -502,16 +500,16 @@ __device__ __forceinline__ void lookback_loop(const ClassifyParams &p, StageBuf<
   CountLookback st{0, 0u};
   Watchdog wd;
   while (true) {
-    const uint32_t sm = km % STAGES;
-    if (k_end == 0xFFFFFFFFu && __all_sync(0xffffffffu, mbar_test_wait(&ctl.marked[sm], (km / STAGES) & 1u))) {
-      StageBuf<TILE> &sb = stages[sm];
-      const int32_t t = sb.tile;
+    const uint32_t mm = km % METAS;
+    if (k_end == 0xFFFFFFFFu && __all_sync(0xffffffffu, mbar_test_wait(&ctl.marked[mm], (km / METAS) & 1u))) {
+      TileMeta<TILE> &tm = metas[mm];
+      const int32_t t = tm.tile;
       if (t < 0) {
         k_end = km;
       } else {
         if (km % kCounterWarps == which) { // own tile: job rows before each range, the tile's count
           const uint32_t tile = (uint32_t)t;
-          const uint32_t c = lane < (uint32_t)kWorkerWarps ? sb.range_cnt[lane] : 0u;
+          const uint32_t c = lane < (uint32_t)kWorkerWarps ? tm.range_cnt[lane] : 0u;
           uint32_t incl = c;
 #pragma unroll
           for (int d = 1; d < kWorkerWarps; d <<= 1) {
@@ -519,9 +517,9 @@ __device__ __forceinline__ void lookback_loop(const ClassifyParams &p, StageBuf<
             if ((int)lane >= d) incl += v;
           }
           const uint32_t total = __shfl_sync(0xffffffffu, incl, kWorkerWarps - 1);
-          if (lane < (uint32_t)kWorkerWarps) sb.range_row[lane] = incl - c; // tile-local until the look-back is done
+          if (lane < (uint32_t)kWorkerWarps) tm.range_row[lane] = incl - c; // tile-local until the look-back is done
           if (lane == 0) {
-            sb.total = total;
+            tm.total = total;
             st_desc_word(&p.desc[tile].c, desc_c(total, tile == 0 ? DESC_INC : DESC_AGG, p.gen));
             if (p.n_tiles == 1) *p.n_jobs = total;
             NXS_TRACE_EVENT(p, EV_COUNT_END, tile);
@@ -534,9 +532,9 @@ __device__ __forceinline__ void lookback_loop(const ClassifyParams &p, StageBuf<
       continue;
     }
     if (kl < km) { // look up the first row index of the oldest own tile (one round trip per poll)
-      const uint32_t sl = kl % STAGES;
-      StageBuf<TILE> &sb = stages[sl];
-      const uint32_t tile = (uint32_t)sb.tile;
+      const uint32_t ml = kl % METAS;
+      TileMeta<TILE> &tm = metas[ml];
+      const uint32_t tile = (uint32_t)tm.tile;
       if (!lb_active) {
         st = CountLookback{(int)tile - 1, 0u};
         lb_active = true;
@@ -544,15 +542,14 @@ __device__ __forceinline__ void lookback_loop(const ClassifyParams &p, StageBuf<
       }
       if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_POLL, tile);
       if (tile == 0 || count_lookback_poll(p, st, lane)) {
-        if (lane < (uint32_t)kWorkerWarps) sb.range_row[lane] += st.excl;
+        if (lane < (uint32_t)kWorkerWarps) tm.range_row[lane] += st.excl;
         if (lane == 0) {
-          const uint32_t total = sb.total;
+          const uint32_t total = tm.total;
           if (tile != 0) st_desc_word(&p.desc[tile].c, desc_c(st.excl + total, DESC_INC, p.gen));
           if (tile == p.n_tiles - 1) *p.n_jobs = (uint64_t)st.excl + total;
-          sb.tile_base = st.excl;
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(&ctl.base_ready[sl]);
+        if (lane == 0) mbar_arrive(&ctl.base_ready[ml]);
         if (lane == 0) NXS_TRACE_EVENT(p, EV_LB_END, tile);
         lb_active = false;
         kl += kCounterWarps;
@@ -566,7 +563,7 @@ __device__ __forceinline__ void lookback_loop(const ClassifyParams &p, StageBuf<
     if (k_end != 0xFFFFFFFFu && kl >= k_end) break; // every own tile is done
     // nothing to do: wait for the next tile to be marked
     if (k_end == 0xFFFFFFFFu) {
-      if (!__all_sync(0xffffffffu, mbar_try_wait(&ctl.marked[sm], (km / STAGES) & 1u, 2000u))) aux_nap<NXS_COUNTER_NS>();
+      if (!__all_sync(0xffffffffu, mbar_try_wait(&ctl.marked[mm], (km / METAS) & 1u, 2000u))) aux_nap<NXS_COUNTER_NS>();
     }
     wd.tick(p.counters + 2);
   }
@@ -676,11 +673,11 @@ __device__ __forceinline__ void sts_u16(uint32_t addr, uint32_t v) {
 
 // ------------------------------------------------------------------ record pass
 // onEvent: guards (:155,:161,:218) and the (kind, reason) switch arms, then superviseAction's order:
-// no checkpoint (:265) -> finished (:276) -> switch (:283).  All of it is table lookups.
+// no checkpoint (:265) -> finished (:276) -> switch (:283).  All of it is table lookups.  On the way
+// the pass leaves what the job pass reads, in place of the columns it consumes (see StageBuf).
 template <int TILE, bool FULL, int STAGES>
-__device__ __forceinline__ void record_pass(const ClassifyParams &p, StageBuf<TILE> *stages, StageBuf<TILE> &sb,
-                                            const Ctl<STAGES> &ctl, Marker<TILE, STAGES> &mk, uint32_t tile,
-                                            uint32_t warp, uint32_t lane) {
+__device__ __forceinline__ void record_pass(const ClassifyParams &p, StageBuf<TILE> &sb, const TileMeta<TILE> &tm,
+                                            const Ctl<STAGES> &ctl, uint32_t tile, uint32_t warp, uint32_t lane) {
   static_assert(TILE % (kWorkerWarps * 32 * kRecordGroup) == 0, "a range is a whole number of record groups");
   constexpr uint32_t RANGE = TILE / kWorkerWarps; // records per warp
   constexpr uint32_t CPW = RANGE / 32;            // 32-record chunks per warp
@@ -689,18 +686,29 @@ __device__ __forceinline__ void record_pass(const ClassifyParams &p, StageBuf<TI
   const uint32_t r0 = warp * RANGE;
   if (!FULL && r0 >= cnt) return; // nothing of the ragged tile falls in this range
   const uint32_t cnt_r = FULL ? RANGE : min(RANGE, cnt - r0); // records of the range that exist
-  // What the job pass reads, written in place of the consumed columns (see StageBuf).
+  if (!FULL) { // a ragged last tile is not sent by the producer: every warp fetches its own range
+    for (uint32_t i = lane; i < cnt_r; i += 32) {
+      sb.keyx[2 + r0 + i] = p.key[start + r0 + i];
+      sb.reason[r0 + i] = p.reason[start + r0 + i];
+      sb.kind[r0 + i] = p.kind[start + r0 + i];
+      sb.flags[r0 + i] = p.flags[start + r0 + i];
+      sb.stage[r0 + i] = p.stage[start + r0 + i];
+    }
+    __syncwarp();
+  }
+  const uint32_t lt = (1u << lane) - 1u;
   uint8_t *const arms = sb.kind + r0;
   MaskRow *const rows_m = reinterpret_cast<MaskRow *>(sb.flags + r0);
   uint32_t *pv = p.verdict + (size_t)start + r0 + lane;
 #pragma unroll 1
   for (uint32_t g = 0; g < CPW; g += kRecordGroup, pv += 32 * kRecordGroup) {
-    NXS_MARK_IF_LANDED();
+    uint2 ti[kRecordGroup];
     uint32_t vt[kRecordGroup], off[kRecordGroup];
     // loads and lookups of the whole group first: the stores below land on bytes read here
 #pragma unroll
     for (uint32_t u = 0; u < kRecordGroup; ++u) {
       const uint32_t i = (g + u) * 32 + lane;
+      ti[u] = tm.tailinfo[r0 / 32 + g + u];
       vt[u] = 0;
       off[u] = 0;
       if (FULL || i < cnt_r) {
@@ -719,15 +727,17 @@ __device__ __forceinline__ void record_pass(const ClassifyParams &p, StageBuf<TI
       const uint32_t FL = ballot_bit(vt[u], VT_FAIL), ER = ballot_bit(vt[u], VT_ERR);
       if (FULL || i < cnt_r) arms[i] = (uint8_t)off[u];
       if (lane == 0) *reinterpret_cast<uint4 *>(rows_m + c) = make_uint4(HE, TM, FL, ER);
+      // the list of the positions (+ 1) where jobs end, from the marker warps' bit masks
+      const uint32_t T = ti[u].x;
+      if ((T >> lane) & 1u) sts_u16(ti[u].y + 2u * __popc(T & lt), i + 1);
     }
   }
 }
 
 // --------------------------------------------------------------------- job pass (a lane per run)
 template <int TILE, bool FULL, int STAGES>
-__device__ __forceinline__ void job_pass(const ClassifyParams &p, StageBuf<TILE> *stages, StageBuf<TILE> &sb,
-                                         const Ctl<STAGES> &ctl, Marker<TILE, STAGES> &mk, uint32_t tile, uint32_t warp,
-                                         uint32_t lane) {
+__device__ __forceinline__ void job_pass(const ClassifyParams &p, StageBuf<TILE> &sb, const TileMeta<TILE> &tm,
+                                         const Ctl<STAGES> &ctl, uint32_t tile, uint32_t warp, uint32_t lane) {
   constexpr uint32_t RANGE = TILE / kWorkerWarps;
   const uint32_t start = tile * TILE;
   const uint32_t cnt = FULL ? (uint32_t)TILE : p.n - start;
@@ -737,21 +747,10 @@ __device__ __forceinline__ void job_pass(const ClassifyParams &p, StageBuf<TILE>
     return;
   }
   const uint32_t cnt_r = FULL ? RANGE : min(RANGE, cnt - r0);
-  // The list of the positions (+ 1) where jobs end, from the marker warps' bit masks, into the
-  // range's slice of the reason column (consumed by the record pass).
-  {
-    constexpr uint32_t CPW = RANGE / 32;
-    const uint32_t lt = (1u << lane) - 1u;
-#pragma unroll
-    for (uint32_t j = 0; j < CPW; ++j) {
-      const uint2 ti = sb.tailinfo[r0 / 32 + j];
-      if ((ti.x >> lane) & 1u) sts_u16(ti.y + 2u * __popc(ti.x & lt), j * 32 + lane + 1);
-    }
-  }
-  const uint32_t njobs = sb.range_cnt[warp];
+  const uint32_t njobs = tm.range_cnt[warp];
   // Does the first record of the range begin a job, does its last record end one?  (warp-uniform)
-  const bool first_is_head = (r0 == 0 ? sb.first_is_head : sb.tailinfo[r0 / 32 - 1].x >> 31) != 0;
-  const bool closed = (sb.tailinfo[(r0 + cnt_r - 1) / 32].x >> ((cnt_r - 1) & 31u)) & 1u;
+  const bool first_is_head = (r0 == 0 ? tm.first_is_head : tm.tailinfo[r0 / 32 - 1].x >> 31) != 0;
+  const bool closed = (tm.tailinfo[(r0 + cnt_r - 1) / 32].x >> ((cnt_r - 1) & 31u)) & 1u;
   // If the range does not end on a job boundary, the end of the range closes the job-end list: the run
   // behind the last job end is the job still open there.  (Then njobs < RANGE, so the entry exists.)
   if (lane == 0) {
@@ -765,13 +764,12 @@ __device__ __forceinline__ void job_pass(const ClassifyParams &p, StageBuf<TILE>
   __syncwarp();
   const uint32_t nruns = njobs + (closed ? 0u : 1u);
   const uint32_t gbase = p.record_base + start + r0; // batch index of the range's first record
-  nxs_job_row *prow = p.rows + ((size_t)sb.range_row[warp] + lane); // row of run `lane`
+  nxs_job_row *prow = p.rows + ((size_t)tm.range_row[warp] + lane); // row of run `lane`
   if (lane < nruns) job_round<TILE, true, STAGES>(p, sb, ctl, warp, r0, lane, njobs, first_is_head, gbase, prow);
 #pragma unroll 1
-  for (uint32_t kb = 32; kb < nruns; kb += 32) {
-    NXS_MARK_IF_LANDED();
+  for (uint32_t k = 32 + lane; k < nruns; k += 32) {
     prow += 32;
-    if (kb + lane < nruns) job_round<TILE, false, STAGES>(p, sb, ctl, warp, r0, kb + lane, njobs, first_is_head, gbase, prow);
+    job_round<TILE, false, STAGES>(p, sb, ctl, warp, r0, k, njobs, first_is_head, gbase, prow);
   }
   // the stage's columns were written here through the generic proxy; the next tile lands in them through the async proxy
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -779,88 +777,77 @@ __device__ __forceinline__ void job_pass(const ClassifyParams &p, StageBuf<TILE>
 }
 
 template <int TILE, int STAGES>
-__device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
-                                            uint32_t warp, uint32_t lane) {
-  uint32_t s = 0, par = 0, k = 0; // next tile to classify: stage, parity, index in the CTA's claim order
-  const uint32_t cols_addr = smem_u32_pinned(&ctl.cols[0]);
-  const uint32_t base_addr = smem_u32_pinned(&ctl.base_ready[0]);
-  const uint32_t done_addr = smem_u32_pinned(&ctl.p1done[0]);
-  Marker<TILE, STAGES> mk;
-  mk.full_a = smem_u32_pinned(&ctl.full[0]);
-  mk.marked_a = smem_u32_pinned(&ctl.marked[0]);
+__device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TILE> *stages, TileMeta<TILE> *metas,
+                                            Ctl<STAGES> &ctl, uint32_t warp, uint32_t lane) {
+  constexpr uint32_t METAS = STAGES + 1;
+  uint32_t s = 0, par = 0, m = 0, mpar = 0; // next tile to classify: stage and slot of the description ring, with parities
+  const uint32_t cols_addr = smem_u32_pinned(&ctl.cols[0]), full_addr = smem_u32_pinned(&ctl.full[0]);
+  const uint32_t claimed_addr = smem_u32_pinned(&ctl.claimed[0]), marked_addr = smem_u32_pinned(&ctl.marked[0]);
+  const uint32_t base_addr = smem_u32_pinned(&ctl.base_ready[0]), done_addr = smem_u32_pinned(&ctl.p1done[0]);
   Watchdog wd;
 #ifdef NXS_TRACE_STATS
   uint64_t st_idle = 0, st_busy = 0, st_idle_base = 0;
 #endif
+  // An idle warp sleeps off the issue slots in a loop kept as short as possible (a barrier test, a
+  // nap): every instruction an idle warp issues is taken from a busy one.
+#define NXS_WORKER_WAIT(addr, parity)                                      \
+  while (!__all_sync(0xffffffffu, mbar_test_wait_a((addr), (parity)))) {   \
+    __nanosleep(NXS_IDLE_NS);                                              \
+    wd.tick(p.counters + 2);                                               \
+  }                                                                        \
+  wd.reset()
   while (true) {
-    // Wait for the tile's columns (the record pass needs neither the keys nor the job boundaries).  An idle
-    // warp sleeps off the issue slots in a loop kept as short as possible (barrier tests, a nap): every
-    // instruction an idle warp issues is taken from a busy one.
 #ifdef NXS_TRACE_STATS
     const uint64_t t_a = global_timer_ns();
 #endif
-    while (!__all_sync(0xffffffffu, mbar_test_wait_a(cols_addr + 8u * s, par))) {
-      NXS_MARK_IF_LANDED();
-      __nanosleep(NXS_IDLE_NS);
-      wd.tick(p.counters + 2);
-    }
+    NXS_WORKER_WAIT(claimed_addr + 8u * m, mpar);
+    const TileMeta<TILE> &tm = metas[m];
+    const int32_t t = tm.tile;
+    if (t < 0) break; // (every role learns the end of the work from the description ring)
+    StageBuf<TILE> &sb = stages[s];
+    const bool full_tile = p.n - (uint32_t)t * TILE >= (uint32_t)TILE;
+    // (1) the record pass: the tile's columns, and (long since there) the marker warps' bit masks
+    NXS_WORKER_WAIT(cols_addr + 8u * s, par);
+    NXS_WORKER_WAIT(marked_addr + 8u * m, mpar);
 #ifdef NXS_TRACE_STATS
     uint64_t t_b = global_timer_ns();
     st_idle += t_b - t_a;
 #endif
-    wd.reset();
-    StageBuf<TILE> &sb = stages[s];
-    const int32_t t = sb.tile;
-    const bool full_tile = t >= 0 && p.n - (uint32_t)t * TILE >= (uint32_t)TILE;
-    // A ragged last tile is copied into the stage by the marking (not by the producer), and the end
-    // marker must be passed on to the look-back warps before this warp leaves: mark up to this tile first.
-    if (!full_tile) {
-      while (mk.km <= k && !mk.done) {
-        NXS_MARK_IF_LANDED();
-        wd.tick(p.counters + 2);
-      }
-      wd.reset();
-    }
-    if (t >= 0) {
-      // (1) the record pass
-      if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_START, (uint32_t)t);
-      if (full_tile) record_pass<TILE, true, STAGES>(p, stages, sb, ctl, mk, (uint32_t)t, warp, lane);
-      else record_pass<TILE, false, STAGES>(p, stages, sb, ctl, mk, (uint32_t)t, warp, lane);
-      __syncwarp();
-      // (2) the job pass, once the look-back has delivered the index of the tile's first job row
+    if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_START, (uint32_t)t);
+    if (full_tile) record_pass<TILE, true, STAGES>(p, sb, tm, ctl, (uint32_t)t, warp, lane);
+    else record_pass<TILE, false, STAGES>(p, sb, tm, ctl, (uint32_t)t, warp, lane);
+    __syncwarp();
+    // (2) the job pass: the index of the tile's first job row (known since before the tile landed) and its keys
 #ifdef NXS_TRACE_STATS
-      const uint64_t t_c = global_timer_ns();
+    const uint64_t t_c = global_timer_ns();
 #endif
-      while (!__all_sync(0xffffffffu, mbar_test_wait_a(base_addr + 8u * s, par))) {
-        NXS_MARK_IF_LANDED();
-        __nanosleep(NXS_IDLE_NS);
-        wd.tick(p.counters + 2);
-      }
+    NXS_WORKER_WAIT(base_addr + 8u * m, mpar);
+    NXS_WORKER_WAIT(full_addr + 8u * s, par);
 #ifdef NXS_TRACE_STATS
-      const uint64_t t_d = global_timer_ns();
-      st_idle += t_d - t_c;
-      st_idle_base += t_d - t_c;
-      t_b += t_d - t_c;
+    const uint64_t t_d = global_timer_ns();
+    st_idle += t_d - t_c;
+    st_idle_base += t_d - t_c;
+    t_b += t_d - t_c;
 #endif
-      wd.reset();
-      if (full_tile) job_pass<TILE, true, STAGES>(p, stages, sb, ctl, mk, (uint32_t)t, warp, lane);
-      else job_pass<TILE, false, STAGES>(p, stages, sb, ctl, mk, (uint32_t)t, warp, lane);
-      if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_END, (uint32_t)t);
-    }
+    if (full_tile) job_pass<TILE, true, STAGES>(p, sb, tm, ctl, (uint32_t)t, warp, lane);
+    else job_pass<TILE, false, STAGES>(p, sb, tm, ctl, (uint32_t)t, warp, lane);
+    if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_END, (uint32_t)t);
     __syncwarp();
 #ifdef NXS_TRACE_STATS
     st_busy += global_timer_ns() - t_b;
-    if (t < 0 && lane == 0) {
-      NXS_TRACE_STAT(p, EV_W_IDLE, (uint32_t)(st_idle >> 4) | warp << 28);
-      NXS_TRACE_STAT(p, EV_W_BUSY, (uint32_t)(st_busy >> 4) | warp << 28);
-      NXS_TRACE_STAT(p, EV_C_IDLE, (uint32_t)(st_idle_base >> 4) | warp << 28);
-    }
 #endif
     if (lane == 0) mbar_arrive_a(done_addr + 8u * s);
-    if (t < 0) break;
-    ++k;
     if (++s == STAGES) s = 0, par ^= 1u;
+    if (++m == METAS) m = 0, mpar ^= 1u;
   }
+#undef NXS_WORKER_WAIT
+#ifdef NXS_TRACE_STATS
+  if (lane == 0) {
+    NXS_TRACE_STAT(p, EV_W_IDLE, (uint32_t)(st_idle >> 4) | warp << 28);
+    NXS_TRACE_STAT(p, EV_W_BUSY, (uint32_t)(st_busy >> 4) | warp << 28);
+    NXS_TRACE_STAT(p, EV_C_IDLE, (uint32_t)(st_idle_base >> 4) | warp << 28);
+  }
+#endif
 }
 
 // ----------------------------------------------------------------- summary warp
@@ -900,25 +887,26 @@ __device__ __forceinline__ bool summ_lookback_poll(const ClassifyParams &p, Summ
 }
 
 template <int TILE, int STAGES>
-__device__ __forceinline__ void summary_loop(const ClassifyParams &p, StageBuf<TILE> *stages, Ctl<STAGES> &ctl,
-                                             uint32_t lane) {
-  uint32_t s = 0, par = 0;
+__device__ __forceinline__ void summary_loop(const ClassifyParams &p, StageBuf<TILE> *stages, TileMeta<TILE> *metas,
+                                             Ctl<STAGES> &ctl, uint32_t lane) {
+  constexpr uint32_t METAS = STAGES + 1;
+  uint32_t s = 0, par = 0, m = 0, mpar = 0; // next tile: stage and slot of the description ring, with parities
   uint32_t q_head = 0, q_tail = 0; // pending tiles: ring [q_head, q_tail)
   bool end = false, lb_active = false;
   SummLookback st{0, summ_identity()};
   Watchdog wd;
   while (true) {
     // A finished tile comes first (frees its stage, publishes its summary) unless the pending ring is full.
+    if (!end && __all_sync(0xffffffffu, mbar_test_wait(&ctl.claimed[m], mpar)) && metas[m].tile < 0) {
+      end = true; // (the end of the work is learnt from the description ring)
+      continue;
+    }
     if (!end && q_tail - q_head < (uint32_t)kPendingSlots &&
+        __all_sync(0xffffffffu, mbar_test_wait(&ctl.claimed[m], mpar)) &&
         __all_sync(0xffffffffu, mbar_test_wait(&ctl.p1done[s], par))) {
       StageBuf<TILE> &sb = stages[s];
-      const int32_t t = sb.tile;
-      if (t < 0) {
-        end = true;
-        wd.reset();
-        continue;
-      }
-      const uint32_t tile = (uint32_t)t;
+      const TileMeta<TILE> &tm = metas[m];
+      const uint32_t tile = (uint32_t)tm.tile;
       if (lane == 0) NXS_TRACE_EVENT(p, EV_SUM_START, tile);
       // lanes 0..7 take over what the workers left for their range, then the stage is free
       const bool mine = lane < (uint32_t)kWorkerWarps;
@@ -927,11 +915,12 @@ __device__ __forceinline__ void summary_loop(const ClassifyParams &p, StageBuf<T
       const bool has_unres = mine && sb.range[lane].has_unres;
       const Summ unres = has_unres ? summ_unpack(sb.range[lane].unres) : summ_identity();
       const uint64_t ukey = has_unres ? sb.range[lane].unres_key : 0ull;
-      const uint32_t rowpos = mine ? sb.range_row[lane] : 0u;
-      const bool first_is_head = sb.first_is_head != 0;
+      const uint32_t rowpos = mine ? tm.range_row[lane] : 0u;
+      const bool first_is_head = tm.first_is_head != 0;
       __syncwarp();
-      if (lane == 0) mbar_arrive(&ctl.freeb[s]);
+      if (lane == 0) mbar_arrive(&ctl.freeb[s]); // (stage and description slot)
       if (++s == STAGES) s = 0, par ^= 1u;
+      if (++m == METAS) m = 0, mpar ^= 1u;
 
       // Which ranges hold the first record of the job they leave open (or end on a job boundary)?
       const uint32_t anch_mask = __ballot_sync(0xffffffffu, mine && (suffix.f & F_ANCHORED));
@@ -1029,8 +1018,8 @@ __device__ __forceinline__ void summary_loop(const ClassifyParams &p, StageBuf<T
       aux_nap<NXS_SUMM_LB_NS>();
     } else if (end) {
       break;
-    } else {
-      if (!__all_sync(0xffffffffu, mbar_try_wait(&ctl.p1done[s], par, 2000u))) aux_nap<NXS_SUMMARY_NS>();
+    } else if (__all_sync(0xffffffffu, mbar_try_wait(&ctl.claimed[m], mpar, 2000u))) {
+      if (metas[m].tile >= 0 && !__all_sync(0xffffffffu, mbar_try_wait(&ctl.p1done[s], par, 2000u))) aux_nap<NXS_SUMMARY_NS>();
     }
     wd.tick(p.counters + 2);
   }
@@ -1046,18 +1035,22 @@ __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__
   // address space, so accesses compile to LDS/STS rather than generic loads)
   extern __shared__ __align__(128) uint8_t smem_raw[];
   StageBuf<TILE> *stages = reinterpret_cast<StageBuf<TILE> *>(smem_raw);
+  TileMeta<TILE> *metas = reinterpret_cast<TileMeta<TILE> *>(smem_raw + sizeof(StageBuf<TILE>) * STAGES);
   // static, so that the addresses of the barriers and tables are immediates in the hot loops
   __shared__ Ctl<STAGES> ctl;
   const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(&ctl.full[s], 2);
+      mbar_init(&ctl.full[s], 1);
       mbar_init(&ctl.cols[s], 1);
-      mbar_init(&ctl.marked[s], kWorkerWarps);
-      mbar_init(&ctl.base_ready[s], 1);
       mbar_init(&ctl.p1done[s], kWorkerWarps);
       mbar_init(&ctl.freeb[s], 1);
+    }
+    for (int m = 0; m < STAGES + 1; ++m) {
+      mbar_init(&ctl.claimed[m], 1);
+      mbar_init(&ctl.marked[m], kMarkerWarps);
+      mbar_init(&ctl.base_ready[m], 1);
     }
     mbar_fence_init();
   }
@@ -1082,11 +1075,12 @@ __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__
   }
   __syncthreads(); // the only CTA-wide barrier
 
-  if (warp < (uint32_t)kWorkerWarps) worker_loop<TILE, STAGES>(p, stages, ctl, warp, lane);
+  if (warp < (uint32_t)kWorkerWarps) worker_loop<TILE, STAGES>(p, stages, metas, ctl, warp, lane);
   else if (warp == (uint32_t)kProducerWarp) {
-    if (lane == 0) producer_loop<TILE, STAGES>(p, stages, ctl);
-  } else if (warp == (uint32_t)kSummaryWarp) summary_loop<TILE, STAGES>(p, stages, ctl, lane);
-  else lookback_loop<TILE, STAGES>(p, stages, ctl, warp - kCounterWarp0, lane);
+    if (lane == 0) producer_loop<TILE, STAGES>(p, stages, metas, ctl);
+  } else if (warp == (uint32_t)kSummaryWarp) summary_loop<TILE, STAGES>(p, stages, metas, ctl, lane);
+  else if (warp < (uint32_t)kMarkerWarp0) lookback_loop<TILE, STAGES>(p, metas, ctl, warp - kCounterWarp0, lane);
+  else marker_loop<TILE, STAGES>(p, stages, metas, ctl, warp - kMarkerWarp0, lane);
 }
 
 #endif // __CUDACC__
