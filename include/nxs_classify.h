@@ -200,6 +200,9 @@ int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *d_in,
                         const nxs_out *d_out);
 /* Number of kernels the ctx has launched so far (bench.py's gpu_launches). */
 uint64_t nxs_launch_count(const nxs_ctx *ctx);
+/* Records per tile of the kernel variant the last classification launch of the ctx used
+ * (the library picks one of its built-in tile sizes from the batch size); 0 before any. */
+int nxs_last_tile(const nxs_ctx *ctx);
 
 /* No counterpart in the reference.  The same classification as
  * nxs_classify_device, for hosts that must not let a

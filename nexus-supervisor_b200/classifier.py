@@ -121,6 +121,11 @@ class Classifier:
     def launches(self):
         return int(self._lib.nxs_launch_count(self._ctx))
 
+    @property
+    def last_tile(self):
+        """Records per tile of the kernel variant the last launch used."""
+        return int(self._lib.nxs_last_tile(self._ctx))
+
     # ------------------------------------------------------------- host path
     def classify(self, cols, out_verdict=None, out_rows=None):
         """cols: dict of numpy arrays kind u8, reason_id u16, flags u8, cur_stage u8, job_key u64.

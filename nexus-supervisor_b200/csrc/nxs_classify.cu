@@ -26,6 +26,7 @@ struct nxs_ctx {
   uint32_t *counters = nullptr;
   uint32_t gen = 0;
   uint64_t launches = 0;
+  int last_tile = 0; // records per tile of the last classification launch
   uint8_t lut[128];
   uint16_t code[8];
   // staging for the host-pointer entry point (allocated on first use): two buffer sets, so the
@@ -97,13 +98,15 @@ template <int TILE> int launch_variant(nxs_ctx *ctx, const ClassifyParams &p, ui
   return NXS_OK;
 }
 
-// Tile size for a batch of n records when NXS_TILE does not force one.  Measured on a B200
-// (scripts/small_batch.py, us per launch, 2048 / 4096 / 8192-record tiles): 2e5 records 10.5 / 15.7 /
-// 20.7, 4e6 68.6 / 38.6 / 43.5, 4e7 296 / 256 / 262, 6e7 423 / 369 / 372, 1e8 733 / 617 / 589: small
-// tiles spread a small batch over more SMs, large tiles mean fewer look-backs and hand-overs.
+// Tile size for a batch of n records when NXS_TILE does not force one.  Measured on a B200 with COLD
+// inputs (scripts/small_batch.py rewrites 512 MB before every launch, so the batch comes from HBM, not
+// from L2; us per launch, 2048 / 4096 / 8192-record tiles): 1e5 records 14.3 / 16.4 / 22.5, 3e5 16.4 /
+// 18.4 / 29.7, 1e6 23.6 / 21.5 / 23.5, 4e6 44.0 / 41.0 / 41.0, 1e7 84.0 / 69.7 / 67.6, 4e7 279 / 220 /
+// 197, 6.4e7 434 / 338 / 289 (profiles/r02_v11_small_batches.txt): small tiles spread a small batch
+// over more SMs, large tiles mean fewer look-backs and hand-overs per record.
 int tile_for_batch(uint64_t n) {
-  if (n <= 300000u) return NXS_TILE_S;
-  if (n <= (64u << 20)) return NXS_TILE_M;
+  if (n <= 500000u) return NXS_TILE_S;
+  if (n <= 6000000u) return NXS_TILE_M;
   return NXS_TILE_L;
 }
 
@@ -232,6 +235,7 @@ int nxs_sync(nxs_ctx *ctx) {
 }
 
 uint64_t nxs_launch_count(const nxs_ctx *ctx) { return ctx ? ctx->launches : 0; }
+int nxs_last_tile(const nxs_ctx *ctx) { return ctx ? ctx->last_tile : 0; }
 
 static int launch_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out, uint32_t record_base);
 
@@ -298,7 +302,10 @@ static int launch_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out
   if (tile == NXS_TILE_S) rc = launch_variant<NXS_TILE_S>(ctx, p, grid);
   else if (tile == NXS_TILE_M) rc = launch_variant<NXS_TILE_M>(ctx, p, grid);
   else rc = launch_variant<NXS_TILE_L>(ctx, p, grid);
-  if (rc == NXS_OK) ctx->launches += 1;
+  if (rc == NXS_OK) {
+    ctx->launches += 1;
+    ctx->last_tile = tile;
+  }
   return rc;
 }
 

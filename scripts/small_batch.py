@@ -1,6 +1,8 @@
 #!/usr/bin/env python3
 """Launch latency of nxs_classify_device for small and medium batches (device-resident, CUDA events),
-per built-in tile size (NXS_TILE).  Needs a GPU."""
+per built-in tile size (NXS_TILE).  Two figures per size: back-to-back relaunches over the same buffers
+(which stay in the 126 MB L2 below a few million records) and COLD launches — a 512 MB buffer is
+rewritten before every launch, so inputs come from HBM.  Needs a GPU."""
 import os
 import subprocess
 import sys
@@ -27,6 +29,7 @@ def one(tile):
     rows = torch.empty((cap, 2), dtype=torch.int64, device="cuda")
     nj = torch.zeros(1, dtype=torch.int64, device="cuda")
     out = []
+    flush = torch.zeros(128 << 20, dtype=torch.int32, device="cuda")
     for n in sizes:
         def step():
             clf.classify_device(n, ptr["kind"], ptr["reason_id"], ptr["flags"], ptr["cur_stage"], ptr["job_key"],
@@ -41,8 +44,18 @@ def one(tile):
             step()
         e1.record(stream)
         torch.cuda.synchronize()
-        out.append(e0.elapsed_time(e1) / reps * 1e3)
-    print(f"TILE {tile:>5}: " + "  ".join(f"n={n:>9,}: {us:8.1f} us" for n, us in zip(sizes, out)))
+        warm = e0.elapsed_time(e1) / reps * 1e3
+        cold = []
+        for _ in range(12):
+            flush.add_(1)  # 512 MB read + written: evicts the batch from L2
+            e0.record(stream)
+            step()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            cold.append(e0.elapsed_time(e1) * 1e3)
+        out.append((warm, float(sorted(cold)[len(cold) // 2])))
+    print(f"TILE {tile:>5}: " + "  ".join(f"n={n:>9,}: {w:7.1f} / {c:7.1f} us" for n, (w, c) in zip(sizes, out)) +
+          "   (relaunch / cold median)")
 
 
 if __name__ == "__main__":
