@@ -15,7 +15,9 @@ elements/s by default, .helm/values.yaml:153); this measures the classification 
 Prints ONE JSON line (rank 0).  `value` = records/s with inputs resident in HBM; `e2e` = the same
 through the host-pointer C-ABI call (pinned host buffers, H2D + kernel + D2H inside the timed
 region); `roofline` = algorithmic bytes / kernel time vs the measured HBM copy peak; `cpu_baseline` =
-the C++ oracle port (string-faithful stand-in for the Go loop) on this box's host cores.
+the C++ port of the reference's event loop on this box's host cores (strings built before the clock
+starts); `parity` = every rank's outputs checked against the oracle outside the timed region.
+`--config 1` prints the line of BASELINE configs[1] (1M uniform records) instead.
 """
 import argparse
 import ctypes as C
@@ -47,6 +49,11 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=20_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-pageable", action="store_true")
+    ap.add_argument("--config", type=int, default=2, choices=[1, 2],
+                    help="BASELINE configs[i]: 2 = 1e8 skewed records per GPU (default, the headline), 1 = 1M uniform")
+    ap.add_argument("--parity-records", type=int, default=10_000_000,
+                    help="records of every rank's shard checked against the oracle outside the timed region")
     return ap.parse_args()
 
 
@@ -112,14 +119,55 @@ class ClockSampler:
         return out
 
 
-def cpu_baseline(sample, threads, mode="strings", repeats=3):
-    """Oracle port on the host cores over a bounded sample of the same stream (best of `repeats`)."""
+KERNEL_SOURCES = ("nexus-supervisor_b200/csrc/nxs_kernel.cuh", "nexus-supervisor_b200/csrc/nxs_device.cuh")
+
+
+def kernel_source_hash():
+    """sha256 over the kernel's source files: ties an ncu traffic figure to the build it was taken from."""
+    import hashlib
+    h = hashlib.sha256()
+    for rel in KERNEL_SOURCES:
+        with open(os.path.join(ROOT, rel), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+def measured_traffic(n, tile):
+    """dram bytes per launch from the committed ncu capture — only if it was taken from THIS kernel source,
+    for this record count and tile size; otherwise None (a stale figure is worse than none)."""
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic_per_launch.json")))
+        if tr.get("kernel_source_sha256_16") == kernel_source_hash() and int(tr["records"]) == n and \
+                int(tr.get("tile", 0)) == tile:
+            return tr["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    return None
+
+
+CPU_SAMPLE_NOTE = ("strings pre-materialised before the timed region (in Go they already exist in the *corev1.Event "
+                   "and the informer cache); timed: onEvent's two string switches, one 7-string "
+                   "RunStatusAnalysisResult per handled event, superviseAction's decision against the run's "
+                   "in-memory checkpoint row (services/supervisor.go:159-257,276-370); C++ port, Go toolchain "
+                   "unavailable on this box")
+
+
+def cpu_event_loop(sample, threads, repeats=3):
+    """The reference's CPU loop (C++ port) on the host cores over a bounded sample of the same stream."""
+    from oracle import cpu_oracle
+    cols = cpu_oracle.generate(2, sample)
+    v, _ = cpu_oracle.bench_event_loop(cols, threads=threads, repeats=repeats)
+    return v
+
+
+def cpu_interned(sample, threads, repeats=3):
+    """The same decision on the integer columns the GPU reads (best CPU version of the columnar job)."""
     from oracle import cpu_oracle
     cols = cpu_oracle.generate(2, sample)
     best = None
     for _ in range(repeats):
         t0 = time.perf_counter()
-        cpu_oracle.classify(cols, mode=mode, threads=threads)
+        cpu_oracle.classify(cols, mode="interned", threads=threads)
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
     return len(cols["kind"]) / best
@@ -127,9 +175,8 @@ def cpu_baseline(sample, threads, mode="strings", repeats=3):
 
 def run_reference(args):
     """`--impl reference`: the reference's own CPU algorithm for the path.  The reference is Go and cannot
-    be built here (no Go toolchain, nexus-core not vendored), so this times the C++ oracle port in
-    string-faithful mode — string switches and a 7-string result struct per handled event like
-    RunStatusAnalysisResult — on all host threads.  Each step is a bounded sample of the workload."""
+    be built here (no Go toolchain, nexus-core not vendored), so this times the C++ oracle port of the
+    event loop on all host threads.  Each step is a bounded sample of the workload."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
@@ -139,19 +186,14 @@ def run_reference(args):
     cols = cpu_oracle.generate(2, sample)
     n = len(cols["kind"])
     steps, warmup = max(1, args.steps), max(0, args.warmup)
-    # keep the whole run within a few minutes
-    t0 = time.perf_counter()
-    cpu_oracle.classify(cols, mode="strings", threads=threads)
-    one = time.perf_counter() - t0
-    budget = 150.0
+    one = n / cpu_oracle.bench_event_loop(cols, threads=threads, repeats=1)[0]
+    budget = 120.0  # keep the whole run within a few minutes (string set-up is outside the timed steps)
     if one * (steps + warmup) > budget:
         steps = max(1, int(budget / one) - warmup)
     for _ in range(warmup):
-        cpu_oracle.classify(cols, mode="strings", threads=threads)
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        cpu_oracle.classify(cols, mode="strings", threads=threads)
-    dt = time.perf_counter() - t0
+        cpu_oracle.bench_event_loop(cols, threads=threads, repeats=1)
+    times = [n / cpu_oracle.bench_event_loop(cols, threads=threads, repeats=1)[0] for _ in range(steps)]
+    dt = float(sum(times))
     value = n * steps / dt
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
@@ -159,8 +201,7 @@ def run_reference(args):
         "vs_baseline": None, "dtype": "u8/u16/u64 integer", "data": "synthetic",
         "config": {"workload": WORKLOAD, "records_per_step": n, "note": "bounded sample of the workload"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": f"{n} records of the same stream per step, string-faithful C++ port of "
-                                   "services/supervisor.go:137-374 (Go toolchain unavailable)"},
+                         "sample": f"{n} records of the same stream per step; " + CPU_SAMPLE_NOTE},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -177,6 +218,168 @@ def pinned_array(nx, nbytes, dtype):
     return np.frombuffer(buf, dtype=dtype), p
 
 
+COLUMNS = (("job_key", np.uint64, 8), ("reason_id", np.uint16, 2), ("kind", np.uint8, 1), ("flags", np.uint8, 1),
+           ("cur_stage", np.uint8, 1))
+
+
+def device_columns(torch, cap):
+    raw = torch.empty(cap * 13, dtype=torch.uint8, device="cuda")
+    base = raw.data_ptr()
+    ptr = {"job_key": base, "reason_id": base + cap * 8, "kind": base + cap * 10, "flags": base + cap * 11,
+           "cur_stage": base + cap * 12}
+    return raw, ptr
+
+
+def parity_check(nx, torch, raw, ptr, n, verdict, rows, n_jobs, rank, world, want_records):
+    """Outside the timed region: the first records of this rank's shard, and the job rows they close,
+    against the CPU oracle run on the same (regenerated) records.  Bit for bit."""
+    from oracle import cpu_oracle
+    base = raw.data_ptr()
+    want = cpu_oracle.generate(nx.WORKLOAD_SKEWED, min(want_records * world, n * world), shard=rank, n_shards=world)
+    m = min(len(want["kind"]), n)
+    if m < n:  # the prefix may end inside a job: check whole jobs only
+        k = want["job_key"]
+        while m > 1 and k[m - 1] == k[m - 2]:
+            m -= 1
+        m -= 1
+    if m <= 0:
+        return {"checked_records": 0, "checked_rows": 0, "ok": False}
+    cols = {k: v[:m] for k, v in want.items()}
+    ok = True
+    for name, dt, width in COLUMNS:  # the device generator produced the same records
+        got = raw[ptr[name] - base: ptr[name] - base + m * width].cpu().numpy().view(dt)
+        ok = ok and bool(np.array_equal(got, cols[name]))
+    want_v, want_r = cpu_oracle.classify(cols, threads=min(8, cpu_oracle.hardware_threads()))
+    got_v = verdict[:m].cpu().numpy().view(np.uint32)
+    got_r = rows[:len(want_r)].cpu().numpy().view(np.uint64).reshape(-1, 2).copy().view(cpu_oracle.JOB_ROW).reshape(-1)
+    ok = ok and bool(np.array_equal(got_v, want_v)) and bool(np.array_equal(got_r, want_r)) and len(want_r) <= n_jobs
+    return {"checked_records": int(m), "checked_rows": int(len(want_r)), "ok": bool(ok)}
+
+
+def e2e_run(nx, torch, clf, host_cols, out_v, out_r, steps, barrier):
+    clf.classify(host_cols, out_verdict=out_v, out_rows=out_r)  # warm-up (allocates staging)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        _, r = clf.classify(host_cols, out_verdict=out_v, out_rows=out_r)
+    torch.cuda.synchronize()
+    return time.perf_counter() - t0, len(r)
+
+
+def init_dist(torch, world, local_rank):
+    if world <= 1:
+        return None
+    import torch.distributed as dist
+    # NCCL prints its version banner on fd 1 at the first collective; keep stdout to the one JSON line
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist.barrier()
+        torch.cuda.synchronize()
+    finally:
+        os.dup2(saved, 1)
+        os.close(saved)
+    return dist
+
+
+def run_config1(args, torch, nx, local_rank):
+    """BASELINE configs[1]: 1M uniform records, one record per job, classification only.  One launch is
+    ~17 MB — it would sit in the 126 MB L2 — so the launches rotate over 24 distinct buffer sets (408 MB)
+    and a second figure times single launches after L2 has been overwritten.  Launch-latency-bound."""
+    n, sets = 1_000_000, 24
+    clf = nx.Classifier(device=local_rank, max_records=n)
+    stream = torch.cuda.current_stream()
+    clf.set_stream(stream.cuda_stream)
+    cap = (n + 1023) & ~1023
+    bufs = []
+    for k in range(sets):
+        raw, ptr = device_columns(torch, cap)
+        got = clf.generate_device(nx.WORKLOAD_UNIFORM, n, ptr["kind"], ptr["reason_id"], ptr["flags"],
+                                  ptr["cur_stage"], ptr["job_key"], cap, first=k * n)
+        assert got == n
+        bufs.append((raw, ptr, torch.empty(n, dtype=torch.int32, device="cuda"),
+                     torch.empty((n, 2), dtype=torch.int64, device="cuda")))
+    n_jobs_d = torch.zeros(1, dtype=torch.int64, device="cuda")
+
+    def step(k):
+        raw, ptr, v, r = bufs[k % sets]
+        clf.classify_device(n, ptr["kind"], ptr["reason_id"], ptr["flags"], ptr["cur_stage"], ptr["job_key"],
+                            v.data_ptr(), r.data_ptr(), n_jobs_d.data_ptr())
+
+    steps, warmup = max(args.steps, 200), max(3, args.warmup)
+    for k in range(warmup + sets):
+        step(k)
+    torch.cuda.synchronize()
+    launches0 = clf.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for k in range(steps):
+        step(k)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    gpu_launches = clf.launches - launches0
+    flush = torch.zeros(128 << 20, dtype=torch.int32, device="cuda")
+    cold = []
+    for k in range(15):
+        flush.add_(1)
+        e0.record(stream)
+        step(k)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        cold.append(e0.elapsed_time(e1))
+    cold_ms = float(np.median(cold))
+    # parity of the last buffer set against the oracle
+    from oracle import cpu_oracle
+    raw, ptr, v, r = bufs[(steps - 1) % sets]
+    step(steps - 1)
+    torch.cuda.synchronize()
+    want = cpu_oracle.generate(nx.WORKLOAD_UNIFORM, n, first=((steps - 1) % sets) * n)
+    want_v, want_r = cpu_oracle.classify(want)
+    got_r = r[:n].cpu().numpy().view(np.uint64).reshape(-1, 2).copy().view(cpu_oracle.JOB_ROW).reshape(-1)
+    ok = bool(np.array_equal(v.cpu().numpy().view(np.uint32), want_v)) and bool(np.array_equal(got_r, want_r))
+    # host-pointer call (pinned buffers): H2D + kernel + D2H of one million records
+    host_cols, keep = {}, []
+    base = raw.data_ptr()
+    for name, dt, width in COLUMNS:
+        arr, p = pinned_array(nx, n * width, dt)
+        keep.append(p)
+        arr.view(np.uint8)[:] = raw[ptr[name] - base: ptr[name] - base + n * width].cpu().numpy()
+        host_cols[name] = arr
+    out_v, p1 = pinned_array(nx, n * 4, np.uint32)
+    out_r, p2 = pinned_array(nx, n * 16, nx.JOB_ROW)
+    dt_e2e, jobs = e2e_run(nx, torch, clf, host_cols, out_v, out_r, 20, torch.cuda.synchronize)
+    threads = cpu_oracle.hardware_threads()
+    cpu_v, _ = cpu_oracle.bench_event_loop(want, threads=threads)
+    peak, peak_src = measured_peak()
+    algo = 17.0 * n + 16.0 * n
+    line = {
+        "metric": METRIC, "value": n / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": steps, "warmup": warmup,
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8/u16/u64 integer", "data": "synthetic",
+        "config": {"workload": "uniform_1M (BASELINE configs[1]: 1e6 records, 7 handled (kind, reason) pairs + one "
+                               "unhandled, one record per job)", "records_per_step": n, "jobs_per_step": n,
+                   "l2": f"launches rotate over {sets} distinct buffer sets ({sets * 33 * n // 1000000} MB of inputs and "
+                         "outputs, larger than L2); cold_single_launch_ms: 512 MB rewritten before every launch"},
+        "cold_single_launch_ms": cold_ms, "cold_records_per_s": n / (cold_ms * 1e-3),
+        "e2e": {"value": n * 20 / dt_e2e, "unit": UNIT, "h2d_bytes_per_step": 13 * n, "d2h_bytes_per_step": 20 * n + 8,
+                "ms_per_step": dt_e2e / 20 * 1e3, "api": "nxs_classify (host pointers, pinned)"},
+        "gpu_launches": int(gpu_launches), "parity": {"checked_records": n, "checked_rows": int(len(want_r)), "ok": ok},
+        "roofline": {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": algo / (ms * 1e-3) / 1e9 / peak, "traffic": None,
+                     "kernel": f"nxs::classify_kernel<{clf.last_tile}>", "kernel_ms": ms,
+                     "algorithmic_bytes_per_launch": algo, "bytes_model": "17 B/record + 16 B/job row (one job per record)",
+                     "peak_source": peak_src, "note": "launch-latency-bound: 245 tiles of 4096 records on 148 SMs"},
+        "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"the same {n} records; " + CPU_SAMPLE_NOTE},
+        "note": "classification step only; the supervisor end to end stays I/O-bound",
+    }
+    print(json.dumps(line))
+    return 0
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
@@ -191,20 +394,9 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the classification path has no CPU fallback")
     torch.cuda.set_device(local_rank)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        # NCCL prints its version banner on fd 1 at the first collective; keep stdout to the one JSON line
-        sys.stdout.flush()
-        saved = os.dup(1)
-        os.dup2(2, 1)
-        try:
-            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-            dist.barrier()
-            torch.cuda.synchronize()
-        finally:
-            os.dup2(saved, 1)
-            os.close(saved)
+    if args.config == 1:
+        return run_config1(args, torch, nx, local_rank) if rank == 0 else 0
+    dist = init_dist(torch, world, local_rank)
     if args.gpus != world and rank == 0 and world > 1:
         print(f"warning: --gpus {args.gpus} but WORLD_SIZE {world}", file=sys.stderr)
     n_gpus = world
@@ -215,10 +407,8 @@ def main():
     clf = nx.Classifier(device=local_rank, max_records=cap)
     stream = torch.cuda.current_stream()
     clf.set_stream(stream.cuda_stream)
-    raw = torch.empty(cap * 13, dtype=torch.uint8, device="cuda")
+    raw, ptr = device_columns(torch, cap)
     base = raw.data_ptr()
-    ptr = {"job_key": base, "reason_id": base + cap * 8, "kind": base + cap * 10, "flags": base + cap * 11,
-           "cur_stage": base + cap * 12}
     n = clf.generate_device(nx.WORKLOAD_SKEWED, n_global, ptr["kind"], ptr["reason_id"], ptr["flags"],
                             ptr["cur_stage"], ptr["job_key"], cap, shard=rank, n_shards=n_gpus)
     verdict = torch.empty(n, dtype=torch.int32, device="cuda")
@@ -236,10 +426,12 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(3, args.warmup)):
+    warmup = max(3, args.warmup)
+    for _ in range(warmup):
         step()
     barrier()
     n_jobs = int(n_jobs_d.item())
+    tile = clf.last_tile
     launches0 = clf.launches
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -263,46 +455,56 @@ def main():
         torch.cuda.synchronize()
     clocks = sampler.stop() if rank == 0 else None
 
-    t = torch.tensor([total_ms, float(n), float(n_jobs)], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        tmax = t.clone()
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tsum = t.clone()
-        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        total_ms_max, n_all, jobs_all = float(tmax[0]), float(tsum[1]), float(tsum[2])
-    else:
-        total_ms_max, n_all, jobs_all = total_ms, float(n), float(n_jobs)
+    def reduce(vals, op):
+        t = torch.tensor(vals, dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(t, op=getattr(dist.ReduceOp, op))
+        return [float(x) for x in t]
+
+    total_ms_max, = reduce([total_ms], "MAX")
+    n_all, jobs_all = reduce([float(n), float(n_jobs)], "SUM")
     value = n_all * args.steps / (total_ms_max * 1e-3)
 
-    # ---- end to end through the host-pointer C-ABI call (this rank's shard, pinned host buffers)
+    # ---- parity of this rank's outputs against the oracle (outside every timed region)
+    parity = parity_check(nx, torch, raw, ptr, n, verdict, rows, n_jobs, rank, n_gpus, args.parity_records)
+    p_ok, = reduce([1.0 if parity["ok"] else 0.0], "MIN")
+    p_rec, p_rows = reduce([float(parity["checked_records"]), float(parity["checked_rows"])], "SUM")
+
+    # ---- end to end through the host-pointer C-ABI call (this rank's shard)
     e2e = None
     if not args.no_e2e:
         host_cols, keep = {}, []
-        for name, dt, width in (("job_key", np.uint64, 8), ("reason_id", np.uint16, 2), ("kind", np.uint8, 1),
-                                ("flags", np.uint8, 1), ("cur_stage", np.uint8, 1)):
+        for name, dt, width in COLUMNS:
             arr, p = pinned_array(nx, n * width, dt)
             keep.append(p)
-            src = raw[ptr[name] - base: ptr[name] - base + n * width]
-            arr.view(np.uint8)[:] = src.cpu().numpy()
+            arr.view(np.uint8)[:] = raw[ptr[name] - base: ptr[name] - base + n * width].cpu().numpy()
             host_cols[name] = arr
         out_v, p1 = pinned_array(nx, n * 4, np.uint32)
         out_r, p2 = pinned_array(nx, n * 16, nx.JOB_ROW)
         keep += [p1, p2]
-        clf.classify(host_cols, out_verdict=out_v, out_rows=out_r)  # warm-up (allocates staging)
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.e2e_steps):
-            _, r = clf.classify(host_cols, out_verdict=out_v, out_rows=out_r)
-        torch.cuda.synchronize()
-        dt_e2e = time.perf_counter() - t0
-        te = torch.tensor([dt_e2e], dtype=torch.float64, device="cuda")
-        if dist is not None:
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        assert len(r) == n_jobs
-        e2e = {"value": n_all * args.e2e_steps / float(te[0]), "unit": UNIT, "h2d_bytes_per_step": int(13 * n),
-               "d2h_bytes_per_step": int(4 * n + 16 * n_jobs + 8), "steps": args.e2e_steps,
-               "ms_per_step": float(te[0]) / args.e2e_steps * 1e3,
-               "api": "nxs_classify (host pointers, pinned): 8M-record slices, H2D of the 5 columns, kernel and D2H of verdicts + job rows overlapped on 3 streams"}
+        dt_e2e, got_jobs = e2e_run(nx, torch, clf, host_cols, out_v, out_r, args.e2e_steps, barrier)
+        assert got_jobs == n_jobs
+        dt_max, = reduce([dt_e2e], "MAX")
+        h2d, d2h = int(13 * n), int(4 * n + 16 * n_jobs + 8)
+        link = reduce([h2d * args.e2e_steps / dt_e2e / 1e9, d2h * args.e2e_steps / dt_e2e / 1e9], "MIN") + \
+            reduce([h2d * args.e2e_steps / dt_e2e / 1e9, d2h * args.e2e_steps / dt_e2e / 1e9], "SUM")
+        e2e = {"value": n_all * args.e2e_steps / dt_max, "unit": UNIT, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "steps": args.e2e_steps, "ms_per_step": dt_max / args.e2e_steps * 1e3,
+               "host_buffers": "page-locked (nxs_alloc_host)",
+               "h2d_GBps_per_rank_min": link[0], "d2h_GBps_per_rank_min": link[1],
+               "h2d_GBps_all_ranks": link[2], "d2h_GBps_all_ranks": link[3],
+               "api": "nxs_classify (host pointers): 8M-record slices, H2D of the 5 columns, kernel and D2H of "
+                      "verdicts + job rows overlapped on 3 streams"}
+        if n_gpus == 1 and not args.no_pageable:
+            # the same call with ordinary (pageable) host memory, as a Go caller's slices would be
+            # unless it adopts nxs_alloc_host: the driver stages every copy through its own pinned buffers
+            pg_cols = {k: np.array(v, copy=True) for k, v in host_cols.items()}
+            pg_v, pg_r = np.empty(n, np.uint32), np.empty(n, nx.JOB_ROW)
+            dt_pg, _ = e2e_run(nx, torch, clf, pg_cols, pg_v, pg_r, max(1, args.e2e_steps - 1), barrier)
+            e2e["pageable"] = {"value": n * max(1, args.e2e_steps - 1) / dt_pg, "unit": UNIT,
+                               "ms_per_step": dt_pg / max(1, args.e2e_steps - 1) * 1e3,
+                               "host_buffers": "pageable (numpy arrays)"}
+            assert np.array_equal(pg_v, out_v) and np.array_equal(pg_r[:n_jobs], out_r[:n_jobs])
         for p in keep:
             nx._abi.load().nxs_free_host(p)
 
@@ -317,7 +519,7 @@ def main():
     achieved = algo_bytes / (k_ms * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
-        "warmup": max(3, args.warmup), "ms_per_step": total_ms_max / args.steps, "higher_is_better": True,
+        "warmup": warmup, "ms_per_step": total_ms_max / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8/u16/u64 integer", "data": "synthetic",
         "config": {"workload": WORKLOAD, "records_per_gpu": n, "jobs_per_gpu": n_jobs,
                    "records_total": int(n_all), "jobs_total": int(jobs_all),
@@ -325,34 +527,27 @@ def main():
                    "l2": "inputs larger than L2 (13 B/record x 1e8 = 1.3 GB per pass; no flush needed)",
                    "seed": hex(nx.DEFAULT_SEED)},
         "e2e": e2e, "gpu_launches": int(gpu_launches), "clocks": clocks,
+        "parity": {"checked_records": int(p_rec), "checked_rows": int(p_rows), "ok": bool(p_ok >= 1.0),
+                   "how": "every rank: the first records of its shard and the job rows they close, device "
+                          "output vs the CPU oracle on the regenerated records, bit for bit, outside the timed region"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": "nxs::classify_kernel<%s>" % (os.environ.get("NXS_TILE") or (2048 if n <= 300_000 else 4096 if n <= (64 << 20) else 8192)), "kernel_ms": k_ms,
+                     "traffic": measured_traffic(n, tile), "kernel": f"nxs::classify_kernel<{tile}>", "kernel_ms": k_ms,
                      "algorithmic_bytes_per_launch": algo_bytes,
                      "bytes_model": "17 B/record (13 read + 4 verdict) + 16 B/job row",
-                     "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / 8000.0},
+                     "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / 8000.0,
+                     "kernel_source_sha256_16": kernel_source_hash()},
         "note": "classification step only; the supervisor end to end stays I/O-bound (Kubernetes watches, "
                 "Scylla writes, 10 elements/s default rate limit)",
     }
-    traffic_file = os.path.join(ROOT, "profiles", "traffic_per_launch.json")
-    if os.path.exists(traffic_file):
-        try:
-            tr = json.load(open(traffic_file))
-            if int(tr.get("records", 0)) == n:
-                line["roofline"]["traffic"] = tr["dram_bytes_per_launch"]
-        except Exception:
-            pass
     if not args.no_cpu_baseline and n_gpus == 1:
         from oracle import cpu_oracle
         threads = cpu_oracle.hardware_threads()
         sample = min(args.cpu_sample, n)
-        v_str = cpu_baseline(sample, threads, "strings")
-        v_int = cpu_baseline(sample, threads, "interned")
-        v_str1 = cpu_baseline(max(1, sample // 8), 1, "strings", repeats=1)
         line["cpu_baseline"] = {
-            "value": v_str, "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": f"{sample} records of the same stream, best of 3; string-faithful C++ port of "
-                      "services/supervisor.go:137-374 (stand-in for the Go loop; Go toolchain unavailable)",
-            "interned_all_cores": v_int, "strings_single_thread": v_str1}
+            "value": cpu_event_loop(sample, threads), "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{sample} records of the same stream, best of 3; " + CPU_SAMPLE_NOTE,
+            "interned_all_cores": cpu_interned(sample, threads),
+            "event_loop_single_thread": cpu_event_loop(max(1, sample // 8), 1, repeats=1)}
     print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()

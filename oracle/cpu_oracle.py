@@ -50,6 +50,9 @@ def lib():
         for f in (L.nxo_kind_name, L.nxo_reason_name, L.nxo_stage_name):
             f.restype = C.c_char_p
             f.argtypes = [C.c_uint32]
+        L.nxo_bench_event_loop.restype = C.c_double
+        L.nxo_bench_event_loop.argtypes = [C.c_int, u8p, u16p, u8p, u8p, u64p, C.c_uint64, C.c_uint16, C.c_int,
+                                           u64p, u64p]
         L.nxo_hardware_threads.restype = C.c_uint
         _lib = L
     return _lib
@@ -80,6 +83,18 @@ def classify(cols, finished_mask=FINISHED_MASK_DEFAULT, mode="interned", threads
                             _p(verdict, C.c_uint32) if want_verdict else None,
                             rows.ctypes.data if want_rows else None)
     return verdict, (rows[:nj] if want_rows else nj)
+
+
+def bench_event_loop(cols, threads=1, finished_mask=FINISHED_MASK_DEFAULT, repeats=3):
+    """Timed stand-in for the Go loop: onEvent's string switches + one 7-string result per handled event +
+    superviseAction's decision against the run's in-memory row; the events' strings are built before the
+    clock starts (in Go they already exist in the *corev1.Event).  Returns (records/s, handled events)."""
+    kind, reason, flags, stage, key = _cols(cols)
+    handled, checksum = C.c_uint64(0), C.c_uint64(0)
+    dt = lib().nxo_bench_event_loop(threads, _p(kind, C.c_uint8), _p(reason, C.c_uint16), _p(flags, C.c_uint8),
+                                    _p(stage, C.c_uint8), _p(key, C.c_uint64), len(kind), finished_mask, repeats,
+                                    C.byref(handled), C.byref(checksum))
+    return len(kind) / dt, int(handled.value)
 
 
 def generate(workload, n, seed=0x6E65787573, first=0, shard=0, n_shards=1):

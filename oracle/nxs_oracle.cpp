@@ -27,6 +27,7 @@
 // Build: see oracle/Makefile (g++ -O3 -march=native -shared -fPIC).
 
 #include <atomic>
+#include <chrono>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -443,6 +444,102 @@ Rec gen_skewed(uint64_t seed, uint64_t i) {
 } // namespace
 
 // =================================================================== C ABI
+// ------------------------------------------------- timed stand-in for the Go loop
+// What services/supervisor.go does per event, and nothing else: the strings of the event and of the
+// cached object EXIST already when onEvent runs (they are fields of *corev1.Event and of the
+// informer's objects, :145,:160,:211), so they are built here before the clock starts.  Timed: the
+// two string switches and the 7-string RunStatusAnalysisResult per handled event (onEvent, :159-257),
+// then superviseAction's decision against the run's checkpoint row held in memory (:264-370:
+// IsFinished, the action switch, the Sprintf of the cause) — one row per job, replayed in record
+// order.  The three network calls of superviseAction are not modelled.
+struct EventStrings {
+  std::string name, uid; // event.InvolvedObject.Name / UID
+};
+struct LoopResult {
+  uint64_t handled = 0, upserts = 0, deletes = 0, checksum = 0;
+};
+LoopResult event_loop(const Columns &c, const EventStrings *strs, uint64_t lo, uint64_t hi,
+                      uint16_t finished_mask) {
+  LoopResult r;
+  Checkpoint job_row;
+  static const std::string_view kAlgorithm = "test-algorithm";
+  for (uint64_t i = lo; i < hi; ++i) {
+    if (i == lo || c.key[i] != c.key[i - 1]) job_row = Checkpoint{stage_name(c.stage[i]), "", ""};
+    const uint8_t kind = c.kind[i], flags = c.flags[i];
+    const uint16_t reason = c.reason[i];
+    const EventStrings &es = strs[i - lo];
+    const Event ev{kind < 3 ? kKindNames[kind] : "Other", reason < 16 ? kReasonNames[reason] : "Unknown", "",
+                   es.uid, es.name};
+    const CachedObject obj{(flags & 2) != 0, es.name, kAlgorithm};
+    const auto res = on_event(ev, (flags & 1) != 0, obj);
+    if (!res) continue;
+    ++r.handled;
+    const ApplyOutcome o = supervise_action(*res, (flags & 4) ? &job_row : nullptr, finished_mask);
+    r.upserts += o.upsert;
+    r.deletes += o.delete_job;
+    r.checksum += job_row.failure_cause.size() + res->RequestId.size();
+  }
+  return r;
+}
+
+extern "C" {
+
+// Best-of-`repeats` wall time of event_loop over the n records, split over `threads` ranges cut on job
+// boundaries; the per-record strings are materialised by each thread before the timed region.
+double nxo_bench_event_loop(int threads, const uint8_t *kind, const uint16_t *reason, const uint8_t *flags,
+                            const uint8_t *stage, const uint64_t *key, uint64_t n, uint16_t finished_mask,
+                            int repeats, uint64_t *handled, uint64_t *checksum) {
+  if (threads < 1) threads = 1;
+  Columns c{kind, reason, flags, stage, key};
+  std::vector<uint64_t> cut(threads + 1, n);
+  cut[0] = 0;
+  for (int t = 1; t < threads; ++t) {
+    uint64_t p = n / threads * t;
+    if (p < cut[t - 1]) p = cut[t - 1];
+    while (p < n && p > 0 && key[p] == key[p - 1]) ++p;
+    cut[t] = p;
+  }
+  std::vector<std::vector<EventStrings>> strs(threads);
+  std::vector<LoopResult> results(threads);
+  std::atomic<int> ready{0}, go{0}, done{0};
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; ++t)
+    pool.emplace_back([&, t] {
+      const uint64_t lo = cut[t], hi = cut[t + 1];
+      strs[t].resize(hi - lo);
+      char buf[40];
+      for (uint64_t i = lo; i < hi; ++i) { // (untimed) what the informer cache already holds
+        snprintf(buf, sizeof buf, "%016llx", (unsigned long long)key[i]);
+        strs[t][i - lo].name = buf;
+        snprintf(buf, sizeof buf, "uid-%llu", (unsigned long long)i);
+        strs[t][i - lo].uid = buf;
+      }
+      for (int rep = 1; rep <= repeats; ++rep) {
+        ready.fetch_add(1);
+        while (go.load(std::memory_order_acquire) < rep) std::this_thread::yield();
+        results[t] = event_loop(c, strs[t].data(), lo, hi, finished_mask);
+        done.fetch_add(1);
+      }
+    });
+  double best = 1e30;
+  for (int rep = 1; rep <= repeats; ++rep) {
+    while (ready.load() < threads * rep) std::this_thread::yield();
+    const auto t0 = std::chrono::steady_clock::now();
+    go.store(rep, std::memory_order_release);
+    while (done.load() < threads * rep) std::this_thread::yield();
+    const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (dt < best) best = dt;
+  }
+  for (auto &th : pool) th.join();
+  uint64_t h = 0, cs = 0;
+  for (const LoopResult &r : results) h += r.handled, cs += r.checksum + r.upserts + r.deletes;
+  if (handled) *handled = h;
+  if (checksum) *checksum = cs;
+  return best;
+}
+
+} // extern "C"
+
 extern "C" {
 
 struct nxo_job_row { uint64_t job_key; uint32_t verdict; uint32_t winner_idx; };

@@ -126,6 +126,53 @@ def test_host_path_slices_on_job_boundaries():
         assert c.launches == 2 * 3
 
 
+def test_host_path_error_after_enqueued_slices_leaves_nothing_in_flight():
+    """A job of four million records straddling a slice cut makes nxs_classify give up with
+    NXS_ERR_CAPACITY after earlier slices have been uploaded, classified and queued for download.  The call
+    must drain its copy streams before it returns: the caller frees (here: poisons and drops) its buffers
+    right away, and the same context then classifies another batch correctly."""
+    import ctypes as C
+    rng = np.random.default_rng(7)
+    n = 20_000_000
+    cols = util.random_cols(rng, n, 5, wide=False)
+    cols["job_key"][15_500_000:19_500_000] = np.uint64(0xABCDEF0123456789)  # one job across the second cut (2 x 8Mi)
+    lib = nx._abi.load()
+    with nx.Classifier(device=0, max_records=n) as c:
+        def pinned(nbytes):
+            p = C.c_void_p()
+            assert lib.nxs_alloc_host(nbytes, C.byref(p)) == 0
+            return p
+        bufs = {k: pinned(v.nbytes) for k, v in cols.items()}
+        for k, v in cols.items():
+            C.memmove(bufs[k], v.ctypes.data, v.nbytes)
+        out_v, out_r = pinned(4 * n), pinned(16 * n)
+        nj = C.c_uint64(0)
+        batch = nx._abi.Batch(bufs["kind"], bufs["reason_id"], bufs["flags"], bufs["cur_stage"], bufs["job_key"], n)
+        out = nx._abi.Out(out_v, out_r, C.addressof(nj))
+        rc = lib.nxs_classify(c._ctx, C.byref(batch), C.byref(out))
+        assert rc == nx._abi.NXS_ERR_CAPACITY, lib.nxs_strerror(rc)
+        assert b"single job" in lib.nxs_last_error(c._ctx)
+        assert c.launches >= 1  # at least one slice had been enqueued before the call gave up
+        for p in list(bufs.values()) + [out_v, out_r]:  # the caller's buffers are its own again: free them now
+            lib.nxs_free_host(p)
+        small = util.random_cols(rng, 3_000_000, 40)
+        util.assert_same(*c.classify(small), *cpu_oracle.classify(small, threads=4), "after the failed call")
+        # the whole batch still goes through the device-resident entry point, as the error text says
+        import torch
+        dev = {k: torch.from_numpy(v.view(np.uint8).copy()).cuda() for k, v in cols.items()}
+        v_d = torch.empty(n, dtype=torch.int32, device="cuda")
+        r_d = torch.empty((n, 2), dtype=torch.int64, device="cuda")
+        n_d = torch.zeros(1, dtype=torch.int64, device="cuda")
+        c.classify_device(n, dev["kind"].data_ptr(), dev["reason_id"].data_ptr(), dev["flags"].data_ptr(),
+                          dev["cur_stage"].data_ptr(), dev["job_key"].data_ptr(), v_d.data_ptr(), r_d.data_ptr(),
+                          n_d.data_ptr())
+        c.sync()
+        want_v, want_r = cpu_oracle.classify(cols, threads=cpu_oracle.hardware_threads())
+        jobs = int(n_d.item())
+        got_r = r_d[:jobs].cpu().numpy().view(np.uint64).reshape(-1, 2).copy().view(cpu_oracle.JOB_ROW).reshape(-1)
+        util.assert_same(v_d.cpu().numpy().view(np.uint32), got_r, want_v, want_r, "device path, 4M-record job")
+
+
 def test_two_contexts_launching_concurrently():
     """Two contexts on one GPU, each on its own stream, launched back to back without synchronising in
     between: the kernels share the SMs, each context has its own tile counter and descriptors."""

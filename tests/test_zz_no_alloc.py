@@ -3,8 +3,9 @@ allocate device memory (their own pool owns the HBM budget, or a cudaMalloc/cuda
 acceptable on their loop).  It keeps the kernel's scratch in a static __device__ array, so every call
 shares that array and must clear what it uses.  The test drives it through the C ABI twice in a row —
 a large batch, then a smaller, different one, so stale descriptors of the first call would show — and
-requires bit-identical output to the ordinary entry point (nxs_classify_device), an unchanged amount of
-free device memory across the second call, and a clean refusal above NXS_NOALLOC_MAX_RECORDS.
+requires bit-identical output to the ordinary entry point (nxs_classify_device) AND to the CPU oracle run
+on the same columns, an unchanged amount of free device memory across the second call, and a clean
+refusal above NXS_NOALLOC_MAX_RECORDS.
 The file name makes pytest collect it last; it also passes when run alone in a fresh process."""
 import ctypes as C
 
@@ -12,6 +13,7 @@ import numpy as np
 import pytest
 
 import nexus_supervisor_b200 as nx
+from oracle import cpu_oracle
 from tests import util
 
 pytestmark = pytest.mark.gpu
@@ -62,6 +64,10 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row():
             assert jobs > 0 and int(got_n.item()) == jobs
             assert torch.equal(got_v, want_v), f"call {call}: verdicts differ"
             assert torch.equal(got_r[:jobs], want_r[:jobs]), f"call {call}: job rows differ"
+            # ... and the oracle, directly (the columns are on the host already)
+            ora_v, ora_r = cpu_oracle.classify(cols, fm, threads=4)
+            host_r = got_r[:jobs].cpu().numpy().view(np.uint64).reshape(-1, 2).copy().view(cpu_oracle.JOB_ROW).reshape(-1)
+            util.assert_same(got_v.cpu().numpy().view(np.uint32), host_r, ora_v, ora_r, f"no-alloc call {call} vs oracle")
             del keep
 
 
