@@ -495,6 +495,25 @@ def main():
                "h2d_GBps_all_ranks": link[2], "d2h_GBps_all_ranks": link[3],
                "api": "nxs_classify (host pointers): 8M-record slices, H2D of the 5 columns, kernel and D2H of "
                       "verdicts + job rows overlapped on 3 streams"}
+        # the wire-lean form of the same call: packed records (10 B up), job rows only (16 B per job down)
+        attr, p3 = pinned_array(nx, n * 2, np.uint16)
+        keep.append(p3)
+        nx.pack_columns(host_cols, out=attr)
+        clf.classify_packed(host_cols["job_key"], attr, out_rows=out_r)  # warm-up
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            _, r_p = clf.classify_packed(host_cols["job_key"], attr, out_rows=out_r)
+        torch.cuda.synchronize()
+        dt_p = time.perf_counter() - t0
+        assert len(r_p) == n_jobs
+        dt_p_max, = reduce([dt_p], "MAX")
+        e2e["packed_rows_only"] = {
+            "value": n_all * args.e2e_steps / dt_p_max, "unit": UNIT, "h2d_bytes_per_step": int(10 * n),
+            "d2h_bytes_per_step": int(16 * n_jobs + 8), "ms_per_step": dt_p_max / args.e2e_steps * 1e3,
+            "api": "nxs_classify_packed (job_key u64 + attr u16), out->verdict = NULL: the consumer acts on job rows",
+            "bytes_model": "10 B/record up + 16 B/job row down over PCIe; on the device 10 B + 7 B (attr expansion) + "
+                           "13 B read + 16 B/job row"}
         if n_gpus == 1 and not args.no_pageable:
             # the same call with ordinary (pageable) host memory, as a Go caller's slices would be
             # unless it adopts nxs_alloc_host: the driver stages every copy through its own pinned buffers

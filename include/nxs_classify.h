@@ -165,8 +165,29 @@ typedef struct nxs_batch {
   uint64_t n;                /* records; < 2^32 - 1                          */
 } nxs_batch;
 
+/* The same record in 10 bytes instead of 13, for callers whose batches cross PCIe: the four small
+ * columns folded into one u16.  Interning already bounds the values, so nothing is lost:
+ *   bits  0-5  reason id, ids >= 63 stored as 63   (ids >= 32 all fall into `default`, :205,:254)
+ *   bits  6-7  kind, kinds >= 3 stored as 3        (neither Job nor Pod, :159,:210)
+ *   bits  8-10 flags (NXS_FLAG_*)
+ *   bits 11-14 checkpoint stage id & 15
+ * The verdict of a packed record is the verdict of the record it was packed from. */
+#define NXS_ATTR_PACK(kind, reason, flags, stage)                                                   \
+  (((uint32_t)(reason) > 63u ? 63u : (uint32_t)(reason)) | ((uint32_t)(kind) > 3u ? 3u : (uint32_t)(kind)) << 6 | \
+   ((uint32_t)(flags) & 7u) << 8 | ((uint32_t)(stage) & 15u) << 11)
+#define NXS_ATTR_REASON(a) ((uint32_t)(a) & 63u)
+#define NXS_ATTR_KIND(a) (((uint32_t)(a) >> 6) & 3u)
+#define NXS_ATTR_FLAGS(a) (((uint32_t)(a) >> 8) & 7u)
+#define NXS_ATTR_STAGE(a) (((uint32_t)(a) >> 11) & 15u)
+typedef struct nxs_batch_packed {
+  const uint64_t *job_key; /* as in nxs_batch                                */
+  const uint16_t *attr;    /* NXS_ATTR_PACK(kind, reason_id, flags, cur_stage) */
+  uint64_t n;
+} nxs_batch_packed;
+
 typedef struct nxs_out {
-  uint32_t *verdict;     /* n                                               */
+  uint32_t *verdict;     /* n; may be NULL: per-record verdicts are then not produced
+                            (nxs_classify, nxs_classify_packed, nxs_classify_device)  */
   nxs_job_row *job_rows; /* capacity >= number of jobs (n is always enough) */
   uint64_t *n_jobs;      /* 1 element                                       */
 } nxs_out;
@@ -194,6 +215,13 @@ int nxs_abi_version(void);
  * Host pointers; copies in, classifies on the GPU, copies verdicts, job rows and
  * the job count back before returning. */
 int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out);
+/* The same for a packed batch (host pointers): 10 instead of 13 bytes per record go up, and with
+ * out->verdict == NULL only the job rows come down — the layout for callers behind PCIe, who act
+ * on job rows anyway.  The attr column is expanded into the four byte columns on the device. */
+int nxs_classify_packed(nxs_ctx *ctx, const nxs_batch_packed *in, const nxs_out *out);
+/* Host helper of the flattening layer: attr[i] = NXS_ATTR_PACK(kind[i], reason_id[i], flags[i], cur_stage[i]). */
+void nxs_pack_columns(const uint8_t *kind, const uint16_t *reason_id, const uint8_t *flags,
+                      const uint8_t *cur_stage, uint64_t n, uint16_t *attr);
 /* Same with DEVICE pointers (16-byte aligned columns); asynchronous on the ctx
  * stream.  out->n_jobs is a device pointer too. */
 int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *d_in,

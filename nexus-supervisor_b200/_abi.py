@@ -27,6 +27,10 @@ class Batch(C.Structure):
                 ("job_key", C.c_void_p), ("n", C.c_uint64)]
 
 
+class BatchPacked(C.Structure):
+    _fields_ = [("job_key", C.c_void_p), ("attr", C.c_void_p), ("n", C.c_uint64)]
+
+
 class Out(C.Structure):
     _fields_ = [("verdict", C.c_void_p), ("job_rows", C.c_void_p), ("n_jobs", C.c_void_p)]
 
@@ -46,6 +50,8 @@ SIGNATURES = {
     "nxs_last_error": (C.c_char_p, [C.c_void_p]),
     "nxs_abi_version": (C.c_int, []),
     "nxs_classify": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(Out)]),
+    "nxs_classify_packed": (C.c_int, [C.c_void_p, C.POINTER(BatchPacked), C.POINTER(Out)]),
+    "nxs_pack_columns": (None, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
     "nxs_classify_device": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(Out)]),
     "nxs_launch_count": (C.c_uint64, [C.c_void_p]),
     "nxs_last_tile": (C.c_int, [C.c_void_p]),

@@ -42,6 +42,18 @@ def unpack_verdict(v):
             "err": (v >> 15) & 3}
 
 
+def pack_columns(cols, out=None):
+    """attr u16 per record = NXS_ATTR_PACK(kind, reason_id, flags, cur_stage) (nxs_pack_columns)."""
+    kind = np.ascontiguousarray(cols["kind"], dtype=np.uint8)
+    reason = np.ascontiguousarray(cols["reason_id"], dtype=np.uint16)
+    flags = np.ascontiguousarray(cols["flags"], dtype=np.uint8)
+    stage = np.ascontiguousarray(cols["cur_stage"], dtype=np.uint8)
+    attr = out if out is not None else np.empty(len(kind), dtype=np.uint16)
+    _abi.load().nxs_pack_columns(kind.ctypes.data, reason.ctypes.data, flags.ctypes.data, stage.ctypes.data, len(kind),
+                                 attr.ctypes.data)
+    return attr
+
+
 def shard_of(job_key, n_shards):
     return _abi.load().nxs_shard_of(int(job_key), int(n_shards))
 
@@ -127,9 +139,12 @@ class Classifier:
         return int(self._lib.nxs_last_tile(self._ctx))
 
     # ------------------------------------------------------------- host path
-    def classify(self, cols, out_verdict=None, out_rows=None):
+    def classify(self, cols, out_verdict=None, out_rows=None, want_verdict=True):
         """cols: dict of numpy arrays kind u8, reason_id u16, flags u8, cur_stage u8, job_key u64.
-        Returns (verdict u32[n], rows JOB_ROW[n_jobs])."""
+        Returns (verdict u32[n], rows JOB_ROW[n_jobs]); verdict is None with want_verdict=False (the
+        per-record verdicts are then neither produced nor copied back)."""
+        if not want_verdict:
+            return self._classify_rows_only(cols, out_rows)
         kind = np.ascontiguousarray(cols["kind"], dtype=np.uint8)
         reason = np.ascontiguousarray(cols["reason_id"], dtype=np.uint16)
         flags = np.ascontiguousarray(cols["flags"], dtype=np.uint8)
@@ -146,6 +161,39 @@ class Classifier:
         out = _abi.Out(verdict.ctypes.data, rows.ctypes.data, C.addressof(n_jobs))
         self._check(self._lib.nxs_classify(self._ctx, C.byref(batch), C.byref(out)))
         return verdict[:n], rows[:n_jobs.value]
+
+    def _classify_rows_only(self, cols, out_rows=None):
+        kind = np.ascontiguousarray(cols["kind"], dtype=np.uint8)
+        reason = np.ascontiguousarray(cols["reason_id"], dtype=np.uint16)
+        flags = np.ascontiguousarray(cols["flags"], dtype=np.uint8)
+        stage = np.ascontiguousarray(cols["cur_stage"], dtype=np.uint8)
+        key = np.ascontiguousarray(cols["job_key"], dtype=np.uint64)
+        n = len(kind)
+        rows = out_rows if out_rows is not None else np.empty(n, dtype=JOB_ROW)
+        n_jobs = C.c_uint64(0)
+        batch = _abi.Batch(kind.ctypes.data, reason.ctypes.data, flags.ctypes.data, stage.ctypes.data,
+                           key.ctypes.data, n)
+        out = _abi.Out(None, rows.ctypes.data, C.addressof(n_jobs))
+        self._check(self._lib.nxs_classify(self._ctx, C.byref(batch), C.byref(out)))
+        return None, rows[:n_jobs.value]
+
+    def classify_packed(self, job_key, attr, out_verdict=None, out_rows=None, want_verdict=False):
+        """Packed batch (job_key u64 + attr u16, see pack_columns): 10 bytes per record go to the GPU; by
+        default only the job rows come back.  Returns (verdict or None, rows)."""
+        key = np.ascontiguousarray(job_key, dtype=np.uint64)
+        attr = np.ascontiguousarray(attr, dtype=np.uint16)
+        n = len(key)
+        if len(attr) != n:
+            raise ValueError("columns differ in length")
+        verdict = None
+        if want_verdict:
+            verdict = out_verdict if out_verdict is not None else np.empty(n, dtype=np.uint32)
+        rows = out_rows if out_rows is not None else np.empty(n, dtype=JOB_ROW)
+        n_jobs = C.c_uint64(0)
+        batch = _abi.BatchPacked(key.ctypes.data, attr.ctypes.data, n)
+        out = _abi.Out(verdict.ctypes.data if want_verdict else None, rows.ctypes.data, C.addressof(n_jobs))
+        self._check(self._lib.nxs_classify_packed(self._ctx, C.byref(batch), C.byref(out)))
+        return (verdict[:n] if want_verdict else None), rows[:n_jobs.value]
 
     # ----------------------------------------------------------- device path
     def classify_device(self, n, kind, reason_id, flags, cur_stage, job_key, verdict, job_rows, n_jobs):

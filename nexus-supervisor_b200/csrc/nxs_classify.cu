@@ -1,5 +1,6 @@
 // nxs_classify.cu — context, launch logic and the C ABI declared in
 // include/nxs_classify.h.  The GPU path is the only path: no CPU fallback.
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -111,6 +112,20 @@ int tile_for_batch(uint64_t n) {
 }
 
 bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// nxs_batch_packed on the device: attr (u16 per record) -> the four byte-wide columns the classification
+// kernel reads.  `reason` may alias `attr` (same index, same width).  7 bytes of HBM traffic per record —
+// next to nothing beside the PCIe transfer the packed layout exists to shorten.
+__global__ void expand_attr_kernel(const uint16_t *attr, uint64_t n, uint16_t *reason, uint8_t *kind, uint8_t *flags,
+                                   uint8_t *stage) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t a = attr[i];
+    reason[i] = (uint16_t)NXS_ATTR_REASON(a);
+    kind[i] = (uint8_t)NXS_ATTR_KIND(a);
+    flags[i] = (uint8_t)NXS_ATTR_FLAGS(a);
+    stage[i] = (uint8_t)NXS_ATTR_STAGE(a);
+  }
+}
 
 } // namespace
 
@@ -259,8 +274,7 @@ static int launch_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out
     NXS_CUDA(ctx, cudaMemsetAsync(out->n_jobs, 0, sizeof(uint64_t), ctx->stream));
     return NXS_OK;
   }
-  if (!in->kind || !in->reason_id || !in->flags || !in->cur_stage || !in->job_key || !out->verdict ||
-      !out->job_rows)
+  if (!in->kind || !in->reason_id || !in->flags || !in->cur_stage || !in->job_key || !out->job_rows)
     return fail_arg(ctx, "null column pointer");
   if (!aligned16(in->kind) || !aligned16(in->reason_id) || !aligned16(in->flags) || !aligned16(in->cur_stage) ||
       !aligned16(in->job_key) || !aligned16(out->job_rows) || (reinterpret_cast<uintptr_t>(out->verdict) & 3u))
@@ -350,7 +364,9 @@ static int ensure_staging(nxs_ctx *ctx, uint64_t slice) {
 // (copy stream 1) while slice k is classified (ctx stream) and slice k-1 is downloaded (copy stream
 // 2), with two device buffer sets.  Job rows of consecutive slices are appended in the caller's
 // buffer, so a slice's rows are downloaded once the job count of the previous one is known.
-static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out, uint64_t slice_cap) {
+// `attr` != nullptr: the batch is packed (job_key + attr); the four small columns of `in` are unused.
+static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *attr, const nxs_out *out,
+                           uint64_t slice_cap) {
   const uint64_t n = in->n;
   const uint64_t cap = ctx->staged_records;
   cudaStream_t s_comp = ctx->stream;
@@ -396,15 +412,25 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out
     // upload (after the previous user of this buffer set has been fully downloaded)
     NXS_CUDA(ctx, cudaStreamWaitEvent(ctx->s_h2d, ctx->e_d2h[b], 0));
     NXS_CUDA(ctx, cudaMemcpyAsync(d_key, in->job_key + lo, m * 8, cudaMemcpyHostToDevice, ctx->s_h2d));
-    NXS_CUDA(ctx, cudaMemcpyAsync(d_reason, in->reason_id + lo, m * 2, cudaMemcpyHostToDevice, ctx->s_h2d));
-    NXS_CUDA(ctx, cudaMemcpyAsync(d_kind, in->kind + lo, m, cudaMemcpyHostToDevice, ctx->s_h2d));
-    NXS_CUDA(ctx, cudaMemcpyAsync(d_flags, in->flags + lo, m, cudaMemcpyHostToDevice, ctx->s_h2d));
-    NXS_CUDA(ctx, cudaMemcpyAsync(d_stage, in->cur_stage + lo, m, cudaMemcpyHostToDevice, ctx->s_h2d));
+    if (attr) { // packed: 10 bytes per record on the wire instead of 13
+      NXS_CUDA(ctx, cudaMemcpyAsync(d_reason, attr + lo, m * 2, cudaMemcpyHostToDevice, ctx->s_h2d));
+    } else {
+      NXS_CUDA(ctx, cudaMemcpyAsync(d_reason, in->reason_id + lo, m * 2, cudaMemcpyHostToDevice, ctx->s_h2d));
+      NXS_CUDA(ctx, cudaMemcpyAsync(d_kind, in->kind + lo, m, cudaMemcpyHostToDevice, ctx->s_h2d));
+      NXS_CUDA(ctx, cudaMemcpyAsync(d_flags, in->flags + lo, m, cudaMemcpyHostToDevice, ctx->s_h2d));
+      NXS_CUDA(ctx, cudaMemcpyAsync(d_stage, in->cur_stage + lo, m, cudaMemcpyHostToDevice, ctx->s_h2d));
+    }
     NXS_CUDA(ctx, cudaEventRecord(ctx->e_h2d[b], ctx->s_h2d));
     // classify
     NXS_CUDA(ctx, cudaStreamWaitEvent(s_comp, ctx->e_h2d[b], 0));
+    if (attr) {
+      const unsigned blocks = (unsigned)std::min<uint64_t>((m + 255) / 256, (uint64_t)ctx->num_sms * 16);
+      expand_attr_kernel<<<blocks, 256, 0, s_comp>>>(d_reason, m, d_reason, d_kind, d_flags, d_stage);
+      NXS_CUDA(ctx, cudaGetLastError());
+      ctx->launches += 1;
+    }
     nxs_batch d_in{d_kind, d_reason, d_flags, d_stage, d_key, m};
-    nxs_out d_out{ctx->d_verdict[b], ctx->d_rows[b], ctx->d_njobs + b};
+    nxs_out d_out{out->verdict ? ctx->d_verdict[b] : nullptr, ctx->d_rows[b], ctx->d_njobs + b};
     rc = launch_classify(ctx, &d_in, &d_out, (uint32_t)lo);
     if (rc != NXS_OK) return rc;
     NXS_CUDA(ctx, cudaEventRecord(ctx->e_kernel[b], s_comp));
@@ -438,17 +464,7 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out
   return NXS_OK;
 }
 
-int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
-  if (!ctx || !in || !out) return NXS_ERR_ARG;
-  if (!out->n_jobs) return fail_arg(ctx, "out->n_jobs is null");
-  if (in->n > ctx->max_records) return NXS_ERR_CAPACITY;
-  if (in->n == 0) {
-    *out->n_jobs = 0;
-    return NXS_OK;
-  }
-  if (!in->kind || !in->reason_id || !in->flags || !in->cur_stage || !in->job_key || !out->verdict ||
-      !out->job_rows)
-    return fail_arg(ctx, "null column pointer");
+static int classify_host(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *attr, const nxs_out *out) {
   DeviceGuard guard(ctx->device);
   NXS_CUDA(ctx, guard.status);
   // A slice may grow past kHostSliceRecords to reach the end of its last job; leave room for that.
@@ -462,7 +478,7 @@ int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
   }
   // everything enqueued earlier on the ctx stream must be done before the copy streams touch the staging
   NXS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  rc = classify_slices(ctx, in, out, slice_cap);
+  rc = classify_slices(ctx, in, attr, out, slice_cap);
   if (rc != NXS_OK) {
     // The caller owns its buffers again the moment this returns: nothing queued for an earlier slice
     // (uploads reading the columns, downloads writing verdicts and rows) may outlive the call.
@@ -472,6 +488,37 @@ int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
     cudaGetLastError();
   }
   return rc;
+}
+
+int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
+  if (!ctx || !in || !out) return NXS_ERR_ARG;
+  if (!out->n_jobs) return fail_arg(ctx, "out->n_jobs is null");
+  if (in->n > ctx->max_records) return NXS_ERR_CAPACITY;
+  if (in->n == 0) {
+    *out->n_jobs = 0;
+    return NXS_OK;
+  }
+  if (!in->kind || !in->reason_id || !in->flags || !in->cur_stage || !in->job_key || !out->job_rows)
+    return fail_arg(ctx, "null column pointer");
+  return classify_host(ctx, in, nullptr, out);
+}
+
+int nxs_classify_packed(nxs_ctx *ctx, const nxs_batch_packed *in, const nxs_out *out) {
+  if (!ctx || !in || !out) return NXS_ERR_ARG;
+  if (!out->n_jobs) return fail_arg(ctx, "out->n_jobs is null");
+  if (in->n > ctx->max_records) return NXS_ERR_CAPACITY;
+  if (in->n == 0) {
+    *out->n_jobs = 0;
+    return NXS_OK;
+  }
+  if (!in->job_key || !in->attr || !out->job_rows) return fail_arg(ctx, "null column pointer");
+  const nxs_batch keys{nullptr, nullptr, nullptr, nullptr, in->job_key, in->n};
+  return classify_host(ctx, &keys, in->attr, out);
+}
+
+void nxs_pack_columns(const uint8_t *kind, const uint16_t *reason_id, const uint8_t *flags, const uint8_t *cur_stage,
+                      uint64_t n, uint16_t *attr) {
+  for (uint64_t i = 0; i < n; ++i) attr[i] = (uint16_t)NXS_ATTR_PACK(kind[i], reason_id[i], flags[i], cur_stage[i]);
 }
 
 int nxs_alloc_host(size_t bytes, void **out) {

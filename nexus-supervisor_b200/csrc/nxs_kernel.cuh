@@ -707,6 +707,7 @@ __device__ __forceinline__ void record_pass(const ClassifyParams &p, StageBuf<TI
   const uint32_t lt = (1u << lane) - 1u;
   uint8_t *const arms = sb.kind + r0;
   MaskRow *const rows_m = reinterpret_cast<MaskRow *>(sb.flags + r0);
+  const bool write_verdict = p.verdict != nullptr; // (the per-record verdicts are optional: the job rows drive the I/O)
   uint32_t *pv = p.verdict + (size_t)start + r0 + lane;
 #pragma unroll 1
   for (uint32_t g = 0; g < CPW; g += kRecordGroup, pv += 32 * kRecordGroup) {
@@ -725,7 +726,7 @@ __device__ __forceinline__ void record_pass(const ClassifyParams &p, StageBuf<TI
         const uint32_t l2 = ctl.lut2[st * 8u + (fl & 7u)];
         off[u] = arm4 + l2; // 4 * arm | 32 * gate class | 128 * IsFinished(cur_stage): one byte
         vt[u] = *reinterpret_cast<const uint32_t *>(reinterpret_cast<const uint8_t *>(ctl.vt) + off[u]);
-        __stcs(pv + 32 * u, vt[u] & kVerdictMask);
+        if (write_verdict) __stcs(pv + 32 * u, vt[u] & kVerdictMask);
       }
     }
 #pragma unroll

@@ -1,0 +1,62 @@
+"""GPU parity tests of the packed batch type (job_key u64 + attr u16) and of the rows-only mode
+(out->verdict == NULL): both exist to cut the bytes that cross PCIe, and both must give exactly what the
+oracle gives for the unpacked columns."""
+import numpy as np
+import pytest
+
+import nexus_supervisor_b200 as nx
+from oracle import cpu_oracle
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("fm", [util.FM_DEFAULT, 0, 0x5A5A])
+def test_packed_exhaustive_domain(fm):
+    """Every (kind 0..4, reason 0..33 / 255 / 256 / 65535, flags 0..7, stage 0..15): packing clamps kinds >= 3
+    and reasons >= 63, which the reference's switches cannot tell from the unclamped values."""
+    with nx.Classifier(device=0, max_records=1 << 18, finished_mask=fm) as c:
+        for per_job in (1, 3):
+            cols = util.exhaustive_cols(per_job)
+            want_v, want_r = cpu_oracle.classify(cols, fm)
+            got_v, got_r = c.classify_packed(cols["job_key"], nx.pack_columns(cols), want_verdict=True)
+            util.assert_same(got_v, got_r, want_v, want_r, f"packed fm={fm:#x} per_job={per_job}")
+            none_v, rows_only = c.classify_packed(cols["job_key"], nx.pack_columns(cols))
+            assert none_v is None and np.array_equal(rows_only, want_r)
+
+
+def test_packed_and_rows_only_sliced_batches():
+    """20M records: several 8M-record slices through the packed upload and the attr expansion."""
+    rng = np.random.default_rng(41)
+    n = 20_000_003
+    cols = util.random_cols(rng, n, 7)
+    want_v, want_r = cpu_oracle.classify(cols, threads=cpu_oracle.hardware_threads())
+    attr = nx.pack_columns(cols)
+    assert np.array_equal(attr & 63, np.minimum(cols["reason_id"], 63)) and np.array_equal((attr >> 11) & 15, cols["cur_stage"] & 15)
+    with nx.Classifier(device=0, max_records=n) as c:
+        v, r = c.classify_packed(cols["job_key"], attr, want_verdict=True)
+        util.assert_same(v, r, want_v, want_r, "packed, sliced")
+        _, r2 = c.classify_packed(cols["job_key"], attr)
+        assert np.array_equal(r2, want_r)
+        _, r3 = c.classify(cols, want_verdict=False)  # unpacked columns, rows only
+        assert np.array_equal(r3, want_r)
+        v4, r4 = c.classify(cols)  # and the ordinary call still returns both
+        util.assert_same(v4, r4, want_v, want_r, "after rows-only calls")
+
+
+def test_rows_only_device_path():
+    import torch
+    rng = np.random.default_rng(43)
+    n = 3_000_001
+    cols = util.random_cols(rng, n, 30)
+    want_v, want_r = cpu_oracle.classify(cols, threads=4)
+    with nx.Classifier(device=0, max_records=n) as c:
+        dev = {k: torch.from_numpy(v.view(np.uint8).copy()).cuda() for k, v in cols.items()}
+        rows = torch.empty((n, 2), dtype=torch.int64, device="cuda")
+        nj = torch.zeros(1, dtype=torch.int64, device="cuda")
+        c.classify_device(n, dev["kind"].data_ptr(), dev["reason_id"].data_ptr(), dev["flags"].data_ptr(),
+                          dev["cur_stage"].data_ptr(), dev["job_key"].data_ptr(), 0, rows.data_ptr(), nj.data_ptr())
+        c.sync()
+        jobs = int(nj.item())
+        got = rows[:jobs].cpu().numpy().view(np.uint64).reshape(-1, 2).copy().view(cpu_oracle.JOB_ROW).reshape(-1)
+        assert np.array_equal(got, want_r)
