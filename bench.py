@@ -266,6 +266,33 @@ def e2e_run(nx, torch, clf, host_cols, out_v, out_r, steps, barrier):
     return time.perf_counter() - t0, len(r)
 
 
+def events_to_verdicts(raw, ptr, base, m):
+    """The honest "events in -> verdicts applied" rate: the first m records of the stream as Kubernetes-
+    Event-shaped structs of strings through the C++ mirror of the service interface (OnEvent: guards'
+    lookups, interning, run grouping; Flush: ReadCheckpoint per run, nxs_classify, Delete / Upsert per job
+    row into null sinks), one host thread.  nexus-supervisor_b200/host/flatten_bench.cpp."""
+    exe = os.path.join(ROOT, "nexus-supervisor_b200", "lib", "flatten_bench")
+    if not os.path.exists(exe):
+        return {"unavailable": "nexus-supervisor_b200/lib/flatten_bench not built (make -C nexus-supervisor_b200/host)"}
+    with tempfile.TemporaryDirectory() as tmp:
+        src = os.path.join(tmp, "cols.bin")
+        with open(src, "wb") as f:
+            f.write(np.uint64(m).tobytes())
+            for name in ("kind", "reason_id", "flags", "cur_stage", "job_key"):
+                width = {"job_key": 8, "reason_id": 2}.get(name, 1)
+                f.write(raw[ptr[name] - base: ptr[name] - base + m * width].cpu().numpy().tobytes())
+        out = subprocess.run([exe, src, os.path.join(tmp, "rows.bin"), "interleave"], capture_output=True, text=True)
+    if out.returncode != 0:
+        return {"unavailable": (out.stdout + out.stderr)[-200:]}
+    st = json.loads(out.stdout.strip().splitlines()[-1])
+    return {"value": st["events_per_s_total"], "unit": "events/s", "events": st["events"], "runs": st["runs"],
+            "host_threads": 1, "seconds": {k: st[k] for k in ("flatten_s", "read_checkpoints_s", "group_s",
+                                                              "classify_s", "apply_s", "total_s")},
+            "note": "events arrive as structs of strings, two halves of the stream interleaved; cache, checkpoint "
+                    "store and Kubernetes client are in-memory fakes (null sinks): with the real ones the rate is "
+                    "set by their I/O (10 elements/s by default)"}
+
+
 def init_dist(torch, world, local_rank):
     if world <= 1:
         return None
@@ -558,6 +585,8 @@ def main():
         "note": "classification step only; the supervisor end to end stays I/O-bound (Kubernetes watches, "
                 "Scylla writes, 10 elements/s default rate limit)",
     }
+    if n_gpus == 1 and not args.no_e2e:
+        line["e2e_from_events"] = events_to_verdicts(raw, ptr, base, min(n, 1_000_000))
     if not args.no_cpu_baseline and n_gpus == 1:
         from oracle import cpu_oracle
         threads = cpu_oracle.hardware_threads()

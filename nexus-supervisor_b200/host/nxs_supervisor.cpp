@@ -2,6 +2,7 @@
 #include "nxs_supervisor.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cstring>
 #include <cstdio>
 #include <numeric>
@@ -39,103 +40,160 @@ Error Supervisor::Init(const ProcessingConfig &config, uint64_t max_batch) {
   config_ = config;
   nxs_destroy(ctx_);
   ctx_ = nullptr;
+  stage_id_.clear();
+  for (uint8_t s = 0; s < 8; ++s) stage_id_[vocab_.stage_names[s]] = s;
   const int rc = nxs_create(device_, max_batch, vocab_.finished_mask, &ctx_);
   if (rc != NXS_OK) return Error{std::string("nxs_create: ") + nxs_strerror(rc)};
   return Error{};
 }
 
+uint32_t Supervisor::Intern(const std::string &s) {
+  const uint32_t off = (uint32_t)heap_.size();
+  heap_.append(s);
+  return off;
+}
+
+namespace {
+double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+} // namespace
+
 // onEvent, :137-259, minus the two switches (they run on the GPU).
 void Supervisor::OnEvent(const Event &event) {
-  Flat f;
-  f.event = event;
+  Flat f{};
   const bool supervised = cache_->IsNexusRunEvent(event); // :147
   if (supervised) f.flags |= NXS_FLAG_SUPERVISED;
   f.kind = nxs_intern_kind(event.involved_kind.data(), event.involved_kind.size());
   f.reason = nxs_intern_reason(event.reason.data(), event.reason.size());
+  const std::string *request_id = nullptr, *algorithm = nullptr;
+  static const std::string kEmpty;
   if (supervised && (f.kind == NXS_KIND_JOB || f.kind == NXS_KIND_POD)) {
-    const auto obj = cache_->GetCachedObject(event.involved_kind, event.involved_name); // :160, :211
-    if (obj) {
+    if (const CachedObject *obj = cache_->GetCachedObject(event)) { // :160, :211
       f.flags |= NXS_FLAG_FOUND;
-      auto label = [&](const std::string &key) {
+      auto label = [&](const std::string &key) -> const std::string * {
         const auto it = obj->labels.find(key);
-        return it == obj->labels.end() ? std::string() : it->second;
+        return it == obj->labels.end() ? &kEmpty : &it->second;
       };
-      f.algorithm = label(vocab_.JobTemplateNameKey);                                              // :181, :232
-      f.request_id = f.kind == NXS_KIND_JOB ? event.involved_name : label(vocab_.JobNameLabel);    // :180, :231
+      algorithm = label(vocab_.JobTemplateNameKey);                                              // :181, :232
+      request_id = f.kind == NXS_KIND_JOB ? &event.involved_name : label(vocab_.JobNameLabel); // :180, :231
     }
   }
-  // Events that cannot lead to a verdict still travel (the kernel drops them): they keep the batch
-  // index == arrival order, and their job key groups them with nothing.
-  f.job_key = (f.flags & NXS_FLAG_FOUND) ? JobKey(f.algorithm, f.request_id)
-                                         : JobKey("\x01unresolved", event.involved_kind + "/" + event.involved_name);
-  events_.push_back(std::move(f));
+  // Events that cannot lead to a verdict still travel (the kernel drops them): they keep their place
+  // in the batch, and their key groups them with nothing that has a checkpoint.
+  static const std::string kUnresolved = "\x01unresolved";
+  const uint64_t key = request_id ? JobKey(*algorithm, *request_id) : JobKey(kUnresolved, event.involved_kind + "/" + event.involved_name);
+  auto it = run_of_.find(key);
+  if (it == run_of_.end()) {
+    Run r{};
+    r.job_key = key;
+    r.found = request_id != nullptr;
+    if (request_id) {
+      r.req_off = Intern(*request_id), r.req_len = (uint32_t)request_id->size();
+      r.alg_off = Intern(*algorithm), r.alg_len = (uint32_t)algorithm->size();
+    }
+    it = run_of_.emplace(key, (uint32_t)runs_.size()).first;
+    runs_.push_back(r);
+  }
+  f.run = it->second;
+  runs_[f.run].count += 1;
+  f.msg_off = Intern(event.message), f.msg_len = (uint32_t)event.message.size();
+  f.uid_off = Intern(event.involved_uid), f.uid_len = (uint32_t)event.involved_uid.size();
+  events_.push_back(f);
 }
 
 Error Supervisor::Flush(std::vector<AppliedVerdict> *applied) {
   if (applied) applied->clear();
-  last_batch_.clear();
+  stats_ = FlushStats{};
+  last_events_.clear();
+  last_runs_.clear();
   last_verdicts_.clear();
+  last_pos_.clear();
   if (events_.empty()) return Error{};
   if (!ctx_) return Error{"supervisor not initialised"};
-  const size_t n = events_.size();
-
-  // Group the records of one run together, runs in order of first arrival, records in arrival order.
-  std::unordered_map<uint64_t, size_t> first_seen;
-  std::vector<size_t> order(n), rank(n);
-  for (size_t i = 0; i < n; ++i) rank[i] = first_seen.emplace(events_[i].job_key, i).first->second;
-  std::iota(order.begin(), order.end(), size_t(0));
-  std::stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) { return rank[a] < rank[b]; });
+  const size_t n = events_.size(), n_runs = runs_.size();
+  stats_.events = n, stats_.runs = n_runs;
 
   // ReadCheckpoint once per run (:264) — this and the writes below are the supervisor's real cost.
-  std::vector<uint8_t> kind(n), flags(n), stage(n);
-  std::vector<uint16_t> reason(n);
-  std::vector<uint64_t> key(n);
-  std::unordered_map<uint64_t, std::optional<CheckpointedRequest>> row_of; // job -> the row read at :264
-  for (size_t j = 0; j < n; ++j) {
-    const Flat &f = events_[order[j]];
-    kind[j] = f.kind;
-    reason[j] = f.reason;
-    key[j] = f.job_key;
-    uint8_t fl = f.flags, st = 0;
-    if (f.flags & NXS_FLAG_FOUND) {
-      auto it = row_of.find(f.job_key);
-      if (it == row_of.end()) it = row_of.emplace(f.job_key, store_->ReadCheckpoint(f.algorithm, f.request_id)).first;
-      if (it->second) {
-        fl |= NXS_FLAG_CHECKPOINT;
-        for (uint8_t s = 0; s < 8; ++s)
-          if (it->second->lifecycle_stage == vocab_.stage_names[s]) st = s;
-      }
+  double t0 = now_s();
+  std::vector<std::optional<CheckpointedRequest>> row_of(n_runs);
+  std::vector<uint8_t> run_stage(n_runs, 0), run_exists(n_runs, 0);
+  for (size_t r = 0; r < n_runs; ++r) {
+    const Run &run = runs_[r];
+    if (!run.found) continue;
+    row_of[r] = store_->ReadCheckpoint(HeapString(run.alg_off, run.alg_len), HeapString(run.req_off, run.req_len));
+    if (row_of[r]) {
+      run_exists[r] = 1;
+      const auto it = stage_id_.find(row_of[r]->lifecycle_stage);
+      run_stage[r] = it == stage_id_.end() ? 0 : it->second;
     }
-    flags[j] = fl;
-    stage[j] = st;
   }
+  double t1 = now_s();
+  stats_.read_checkpoints_s = t1 - t0;
 
-  std::vector<uint32_t> verdict(n);
-  std::vector<nxs_job_row> rows(n);
+  // The records of a run made adjacent, runs in order of first arrival, records in arrival order: a
+  // counting pass over the run indices (they were handed out in first-arrival order by OnEvent).
+  std::vector<uint32_t> next(n_runs);
+  uint32_t off = 0;
+  for (size_t r = 0; r < n_runs; ++r) {
+    next[r] = off;
+    off += runs_[r].count;
+  }
+  col_kind_.resize(n), col_flags_.resize(n), col_stage_.resize(n), col_reason_.resize(n), col_key_.resize(n);
+  src_.resize(n);
+  last_pos_.resize(n);
+  rows_.resize(n_runs);
+  for (size_t i = 0; i < n; ++i) {
+    const Flat &f = events_[i];
+    const uint32_t j = next[f.run]++;
+    col_kind_[j] = f.kind;
+    col_reason_[j] = f.reason;
+    col_flags_[j] = (uint8_t)(f.flags | (run_exists[f.run] ? NXS_FLAG_CHECKPOINT : 0));
+    col_stage_[j] = run_stage[f.run];
+    col_key_[j] = runs_[f.run].job_key;
+    src_[j] = (uint32_t)i;
+    last_pos_[i] = j;
+  }
+  double t2 = now_s();
+  stats_.group_s = t2 - t1;
+
   uint64_t n_jobs = 0;
-  const nxs_batch in{kind.data(), reason.data(), flags.data(), stage.data(), key.data(), n};
-  const nxs_out out{verdict.data(), rows.data(), &n_jobs};
+  if (keep_verdicts_) col_verdict_.resize(n);
+  const nxs_batch in{col_kind_.data(), col_reason_.data(), col_flags_.data(), col_stage_.data(), col_key_.data(), n};
+  const nxs_out out{keep_verdicts_ ? col_verdict_.data() : nullptr, rows_.data(), &n_jobs};
   const int rc = nxs_classify(ctx_, &in, &out);
   if (rc != NXS_OK) return Error{std::string("nxs_classify: ") + nxs_strerror(rc) + ": " + nxs_last_error(ctx_)};
+  double t3 = now_s();
+  stats_.classify_s = t3 - t2;
+  stats_.job_rows = n_jobs;
+  if (n_jobs != n_runs) return Error{"internal error: job rows and runs of the batch differ in number"};
 
-  // The I/O half of superviseAction, once per run, from the job row.
-  size_t j = 0;
+  // The I/O half of superviseAction, once per run, from the job row (row r belongs to run r).
   for (uint64_t r = 0; r < n_jobs; ++r) {
-    const nxs_job_row &row = rows[r];
-    const size_t begin = j;
-    while (j < n && key[j] == row.job_key) ++j; // the run's records are [begin, j)
-    const Flat &first = events_[order[begin]];
-    if (!(first.flags & NXS_FLAG_FOUND)) continue; // unresolved events carry no run
-    const std::string trace = row.winner_idx != NXS_NO_WINNER ? events_[order[row.winner_idx]].event.message : "";
+    const nxs_job_row &row = rows_[r];
+    const Run &run = runs_[r];
+    if (!run.found || row.verdict == 0) continue; // unresolved events carry no run; nothing handled: nothing to do
+    std::string trace;
+    if (row.winner_idx != NXS_NO_WINNER) {
+      const Flat &w = events_[src_[row.winner_idx]];
+      trace = HeapString(w.msg_off, w.msg_len);
+    }
     AppliedVerdict a;
-    (void)Apply(first.algorithm, first.request_id, row.verdict, trace, row_of[row.job_key], &a);
+    (void)Apply(HeapString(run.alg_off, run.alg_len), HeapString(run.req_off, run.req_len), row.verdict, trace, row_of[r], &a);
     if (applied && (a.deleted_job || a.upserted || a.skipped_finished || a.err)) applied->push_back(std::move(a));
   }
+  stats_.apply_s = now_s() - t3;
+
   // keep the batch for AnalysisResultOf (arrival order)
-  last_verdicts_.assign(n, 0);
-  for (size_t jj = 0; jj < n; ++jj) last_verdicts_[order[jj]] = verdict[jj];
-  last_batch_.swap(events_);
+  if (keep_verdicts_) {
+    last_verdicts_.resize(n);
+    for (size_t i = 0; i < n; ++i) last_verdicts_[i] = col_verdict_[last_pos_[i]];
+  }
+  last_events_.swap(events_);
+  last_runs_.swap(runs_);
+  last_heap_.swap(heap_);
   events_.clear();
+  runs_.clear();
+  heap_.clear();
+  run_of_.clear();
   return Error{};
 }
 
@@ -145,6 +203,7 @@ Error Supervisor::Apply(const std::string &algorithm, const std::string &request
                         AppliedVerdict *out) {
   out->algorithm = algorithm;
   out->request_id = request_id;
+  out->trace = trace;
   out->verdict = verdict;
   if (NXS_V_ERR(verdict) == NXS_ERR_NO_CHECKPOINT) { // :265-273: delete the job, report the read error
     (void)client_->DeleteJob(ns_, request_id);
@@ -251,17 +310,18 @@ std::vector<CheckpointUpdate> EncodeCheckpointRows(const nxs_job_row *rows, uint
 
 RunStatusAnalysisResult Supervisor::AnalysisResultOf(size_t i) const {
   RunStatusAnalysisResult r;
-  if (i >= last_batch_.size()) return r;
+  if (i >= last_events_.size() || i >= last_verdicts_.size()) return r;
   const uint32_t v = last_verdicts_[i];
   if (NXS_V_ACTION(v) == 0) return r;
-  const Flat &f = last_batch_[i];
+  const Flat &f = last_events_[i];
+  const Run &run = last_runs_[f.run];
   r.Action = nxs_action_name(NXS_V_ACTION(v));
   r.RunStatusMessage = nxs_msg_template(NXS_V_MSG_TPL(v));
-  r.RunStatusTrace = f.event.message;
-  r.ObjectUID = f.event.involved_uid;
-  r.ObjectKind = f.event.involved_kind;
-  r.RequestId = f.request_id;
-  r.Algorithm = f.algorithm;
+  r.RunStatusTrace = last_heap_.substr(f.msg_off, f.msg_len);
+  r.ObjectUID = last_heap_.substr(f.uid_off, f.uid_len);
+  r.ObjectKind = f.kind == NXS_KIND_JOB ? "Job" : "Pod"; // (only Job and Pod events are ever handled, :159,:210)
+  r.RequestId = last_heap_.substr(run.req_off, run.req_len);
+  r.Algorithm = last_heap_.substr(run.alg_off, run.alg_len);
   return r;
 }
 

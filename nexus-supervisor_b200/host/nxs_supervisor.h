@@ -24,6 +24,7 @@
 #include <map>
 #include <optional>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "nxs_classify.h"
@@ -46,7 +47,8 @@ class ObjectCache { // resolvers.IsNexusRunEvent (:147) and resolvers.GetCachedO
  public:
   virtual ~ObjectCache() = default;
   virtual bool IsNexusRunEvent(const Event &event) = 0;
-  virtual std::optional<CachedObject> GetCachedObject(const std::string &kind, const std::string &name) = 0;
+  // A pointer INTO the cache (nil when the object is missing), as in the reference: read-only, not retained.
+  virtual const CachedObject *GetCachedObject(const Event &event) = 0;
 };
 class CqlStore { // request.CqlStore: ReadCheckpoint (:264), UpsertCheckpoint (:301,:328,:353,:364)
  public:
@@ -85,6 +87,15 @@ struct Vocabulary {
   uint16_t finished_mask = NXS_FINISHED_MASK_DEFAULT; // stands in for (*CheckpointedRequest).IsFinished()
 };
 
+// Where the time of the last Flush went (seconds): the answer to "does the host side ever see the GPU?"
+struct FlushStats {
+  uint64_t events = 0, runs = 0, job_rows = 0;
+  double read_checkpoints_s = 0; // ReadCheckpoint once per run (:264)
+  double group_s = 0;            // records of a run made adjacent, columns filled
+  double classify_s = 0;         // nxs_classify: H2D + kernel + D2H
+  double apply_s = 0;            // Jobs().Delete / UpsertCheckpoint per job row
+};
+
 struct Error { // mirrors Go's `error`: empty message = nil
   std::string message;
   explicit operator bool() const { return !message.empty(); }
@@ -93,6 +104,7 @@ struct Error { // mirrors Go's `error`: empty message = nil
 // What Flush did for one run (one job row): the observable effects of superviseAction.
 struct AppliedVerdict {
   std::string algorithm, request_id;
+  std::string trace; // event.Message of the winner record (-> algorithm_failure_details), "" if none
   uint32_t verdict = 0;
   bool deleted_job = false, upserted = false, skipped_finished = false;
   Error err; // "no checkpoint ..." mirrors the :265-273 path
@@ -116,6 +128,9 @@ class Supervisor {
   // caller: events it cannot use are dropped.
   void OnEvent(const Event &event);
   size_t PendingEvents() const { return events_.size(); }
+  const FlushStats &LastFlushStats() const { return stats_; }
+  // Per-record verdicts are kept for AnalysisResultOf only when asked for (they cost a 4 B/record download).
+  void KeepRecordVerdicts(bool keep) { keep_verdicts_ = keep; }
 
   // superviseAction (:261) for the whole batch: reads each run's checkpoint, classifies on the GPU,
   // then deletes jobs / upserts checkpoints as the verdicts say.  Returns a non-empty error only for
@@ -131,13 +146,24 @@ class Supervisor {
   RunStatusAnalysisResult AnalysisResultOf(size_t event_index) const;
 
  private:
+  // One event of the batch: ids for the GPU, and where its strings sit in the string heap (SURVEY §8(a)
+  // A0: msg_ref / uid_ref — the strings themselves never leave the host and are copied exactly once).
   struct Flat {
-    Event event;
-    std::string request_id, algorithm;
-    uint8_t kind = 0, flags = 0;
-    uint16_t reason = 0;
-    uint64_t job_key = 0;
+    uint32_t run;              // index into runs_
+    uint32_t msg_off, msg_len; // event.Message -> RunStatusTrace
+    uint32_t uid_off, uid_len; // event.InvolvedObject.UID
+    uint16_t reason;
+    uint8_t kind, flags;
   };
+  // One run (checkpoint row) of the batch, in order of first arrival.
+  struct Run {
+    uint64_t job_key;
+    uint32_t req_off, req_len, alg_off, alg_len; // RequestId / Algorithm in the string heap
+    uint32_t count;                              // events of the run in this batch
+    bool found;                                  // resolved through the informer cache
+  };
+  uint32_t Intern(const std::string &s);
+  std::string HeapString(uint32_t off, uint32_t len) const { return heap_.substr(off, len); }
   Error Apply(const std::string &algorithm, const std::string &request_id, uint32_t verdict,
               const std::string &trace, const std::optional<CheckpointedRequest> &checkpoint, AppliedVerdict *out);
   KubeClient *client_;
@@ -148,8 +174,20 @@ class Supervisor {
   Vocabulary vocab_;
   ProcessingConfig config_;
   nxs_ctx *ctx_ = nullptr;
-  std::vector<Flat> events_, last_batch_;
-  std::vector<uint32_t> last_verdicts_;
+  bool keep_verdicts_ = true;
+  FlushStats stats_;
+  std::string heap_, last_heap_;
+  std::vector<Flat> events_, last_events_;
+  std::vector<Run> runs_, last_runs_;
+  std::unordered_map<uint64_t, uint32_t> run_of_;        // job key -> index into runs_
+  std::unordered_map<std::string, uint8_t> stage_id_;    // lifecycle stage spelling -> id
+  std::vector<uint32_t> last_verdicts_, last_pos_;       // per event of the last batch (arrival order)
+  // batch columns, reused from flush to flush
+  std::vector<uint8_t> col_kind_, col_flags_, col_stage_;
+  std::vector<uint16_t> col_reason_;
+  std::vector<uint64_t> col_key_;
+  std::vector<uint32_t> col_verdict_, src_;
+  std::vector<nxs_job_row> rows_;
 };
 
 uint64_t JobKey(const std::string &algorithm, const std::string &request_id); // hash of the checkpoint PK

@@ -28,10 +28,9 @@ struct FakeCache : ObjectCache { // the informer caches of the fake clientset
     const auto l = it->second.labels.find(kNexusComponentLabel);
     return l != it->second.labels.end() && l->second == kAlgorithmRun;
   }
-  std::optional<CachedObject> GetCachedObject(const std::string &kind, const std::string &name) override {
-    const auto it = objects.find({kind, name});
-    if (it == objects.end()) return std::nullopt;
-    return it->second;
+  const CachedObject *GetCachedObject(const Event &e) override {
+    const auto it = objects.find({e.involved_kind, e.involved_name});
+    return it == objects.end() ? nullptr : &it->second;
   }
 };
 struct FakeStore : CqlStore { // nexus.checkpoints, PRIMARY KEY ((algorithm, id))
