@@ -293,6 +293,27 @@ def events_to_verdicts(raw, ptr, base, m):
                     "set by their I/O (10 elements/s by default)"}
 
 
+def encoder_rate(nx, rows, n, n_jobs, sample_rows=10_000_000, msg_len=24):
+    """nxs_encode_checkpoint_rows (host, all cores) on the first job rows of the run: lifecycle_stage,
+    algorithm_failure_cause and algorithm_failure_details of every upserting row into one arena.  Messages
+    are synthetic, msg_len bytes per record."""
+    m = int(min(n_jobs, sample_rows))
+    host_rows = rows[:m].cpu().numpy().view(np.uint64).reshape(-1, 2).copy().view(nx.JOB_ROW).reshape(-1)
+    win = host_rows["winner_idx"]
+    n_rec = int(min(n, int(win[win != nx.NO_WINNER].max()) + 1)) if (win != nx.NO_WINNER).any() else 1
+    heap = np.full(n_rec * msg_len, 97, np.uint8)
+    offs = np.arange(n_rec + 1, dtype=np.uint64) * np.uint64(msg_len)
+    best, out = None, None
+    for _ in range(3):
+        t0 = time.perf_counter()
+        out = nx.encode_checkpoint_rows(host_rows, heap, offs)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return {"value": m / best, "unit": "job rows/s", "job_rows": m, "updates": int(len(out[2])),
+            "arena_bytes": int(out[0].nbytes), "seconds": best, "host_threads": min(32, os.cpu_count() or 1),
+            "note": f"host code (the events' messages live in host memory); {msg_len}-byte synthetic messages"}
+
+
 def init_dist(torch, world, local_rank):
     if world <= 1:
         return None
@@ -587,6 +608,7 @@ def main():
     }
     if n_gpus == 1 and not args.no_e2e:
         line["e2e_from_events"] = events_to_verdicts(raw, ptr, base, min(n, 1_000_000))
+        line["checkpoint_row_encoder"] = encoder_rate(nx, rows, n, n_jobs)
     if not args.no_cpu_baseline and n_gpus == 1:
         from oracle import cpu_oracle
         threads = cpu_oracle.hardware_threads()

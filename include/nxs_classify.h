@@ -272,6 +272,25 @@ const char *nxs_msg_template(uint32_t idx);
 /* AlgorithmFailureCause formats (:298,:325,:350); idx 0 = NULL (untouched) */
 const char *nxs_cause_template(uint32_t idx);
 
+/* ------------------------------------------- checkpoint-row encoder (host) */
+/* The step right after the classification: for every job row that calls for an upsert, the three
+ * columns of nexus.checkpoints (test-resources/checkpoints.cql:1-23) that superviseAction sets
+ * (services/supervisor.go:297-299, :324-326, :349-351, :362) as bytes, back to back in one arena:
+ *   update u (u = 0 .. *n_updates-1, in job-row order) belongs to job row update_row[u];
+ *   lifecycle_stage          = arena[offsets[3u]   .. offsets[3u+1])   stage name of verdict.new_stage
+ *   algorithm_failure_cause  = arena[offsets[3u+1] .. offsets[3u+2])   cause format applied to the message text
+ *   algorithm_failure_details= arena[offsets[3u+2] .. offsets[3u+3])   Message of the winner event
+ *   update_flags[u] (optional) bit 0: cause / details are SET (else the row keeps its own: ToRunning,
+ *   :361-364, and both ranges are empty); bit 1: the job is also deleted.
+ * Rows that only delete the job, skip or fail produce no update.  msg_heap / msg_offsets (n_records + 1
+ * entries) hold event.Message per batch record; NULL = details empty.  stage_names: 16 spellings, or
+ * NULL for nxs_stage_name().  With arena == NULL and offsets == NULL only *n_updates and *arena_bytes
+ * are computed (size query); offsets needs 3 * n_updates + 1 entries.  Host memory, multi-threaded. */
+int nxs_encode_checkpoint_rows(const nxs_job_row *rows, uint64_t n_rows, const uint8_t *msg_heap,
+                               const uint64_t *msg_offsets, uint64_t n_records, const char *const *stage_names,
+                               uint8_t *arena, uint64_t arena_capacity, uint64_t *offsets, uint32_t *update_row,
+                               uint8_t *update_flags, uint64_t *n_updates, uint64_t *arena_bytes);
+
 /* ------------------------------------------------------------- sharding */
 /* Shard of a job for a G-GPU run: splitmix64(job_key) % n_shards. */
 uint32_t nxs_shard_of(uint64_t job_key, uint32_t n_shards);

@@ -65,6 +65,9 @@ SIGNATURES = {
     "nxs_stage_name": (C.c_char_p, [C.c_uint32]),
     "nxs_msg_template": (C.c_char_p, [C.c_uint32]),
     "nxs_cause_template": (C.c_char_p, [C.c_uint32]),
+    "nxs_encode_checkpoint_rows": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
+                                             C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                             u64p, u64p]),
     "nxs_shard_of": (C.c_uint32, [C.c_uint64, C.c_uint32]),
     "nxs_sharded_create": (C.c_int, [C.c_uint32, C.POINTER(C.c_int), C.c_uint32, C.c_uint64, C.c_uint16,
                                      C.POINTER(C.c_void_p)]),

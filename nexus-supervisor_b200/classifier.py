@@ -54,6 +54,31 @@ def pack_columns(cols, out=None):
     return attr
 
 
+def encode_checkpoint_rows(rows, msg_heap=None, msg_offsets=None):
+    """nxs_encode_checkpoint_rows: (arena u8[], offsets u64[3u+1], update_row u32[u], update_flags u8[u]) for the
+    job rows that upsert.  msg_heap / msg_offsets: the events' Message bytes per batch record."""
+    lib = _abi.load()
+    rows = np.ascontiguousarray(rows, dtype=JOB_ROW)
+    n_rec = 0 if msg_offsets is None else len(msg_offsets) - 1
+    heap_p = None if msg_heap is None else np.ascontiguousarray(msg_heap, dtype=np.uint8).ctypes.data
+    offs_p = None if msg_offsets is None else np.ascontiguousarray(msg_offsets, dtype=np.uint64).ctypes.data
+    n_up, n_bytes = C.c_uint64(0), C.c_uint64(0)
+    rc = lib.nxs_encode_checkpoint_rows(rows.ctypes.data, len(rows), heap_p, offs_p, n_rec, None, None, 0, None, None,
+                                        None, C.byref(n_up), C.byref(n_bytes))
+    if rc != _abi.NXS_OK:
+        raise NxsError(rc, "nxs_encode_checkpoint_rows (size query)")
+    arena = np.empty(n_bytes.value, dtype=np.uint8)
+    offsets = np.empty(3 * n_up.value + 1, dtype=np.uint64)
+    update_row = np.empty(n_up.value, dtype=np.uint32)
+    update_flags = np.empty(n_up.value, dtype=np.uint8)
+    rc = lib.nxs_encode_checkpoint_rows(rows.ctypes.data, len(rows), heap_p, offs_p, n_rec, None, arena.ctypes.data,
+                                        arena.nbytes, offsets.ctypes.data, update_row.ctypes.data,
+                                        update_flags.ctypes.data, C.byref(n_up), C.byref(n_bytes))
+    if rc != _abi.NXS_OK:
+        raise NxsError(rc, "nxs_encode_checkpoint_rows")
+    return arena, offsets, update_row, update_flags
+
+
 def shard_of(job_key, n_shards):
     return _abi.load().nxs_shard_of(int(job_key), int(n_shards))
 

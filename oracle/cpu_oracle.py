@@ -53,6 +53,9 @@ def lib():
         L.nxo_bench_event_loop.restype = C.c_double
         L.nxo_bench_event_loop.argtypes = [C.c_int, u8p, u16p, u8p, u8p, u64p, C.c_uint64, C.c_uint16, C.c_int,
                                            u64p, u64p]
+        L.nxo_encode_strings.restype = C.c_uint64
+        L.nxo_encode_strings.argtypes = [u8p, u16p, u8p, u8p, u64p, C.c_uint64, C.c_uint16, C.c_void_p, C.c_uint64,
+                                         C.c_void_p, C.c_void_p, u64p]
         L.nxo_hardware_threads.restype = C.c_uint
         _lib = L
     return _lib
@@ -95,6 +98,23 @@ def bench_event_loop(cols, threads=1, finished_mask=FINISHED_MASK_DEFAULT, repea
                                     _p(stage, C.c_uint8), _p(key, C.c_uint64), len(kind), finished_mask, repeats,
                                     C.byref(handled), C.byref(checksum))
     return len(kind) / dt, int(handled.value)
+
+
+def encode_strings(cols, finished_mask=FINISHED_MASK_DEFAULT, bytes_per_record=48):
+    """What the reference would have written, from the string-mode replay: (arena, offsets, update_job) with
+    lifecycle_stage / algorithm_failure_cause / algorithm_failure_details of every upserted job back to back;
+    event.Message of record i is "m<i>"."""
+    kind, reason, flags, stage, key = _cols(cols)
+    n = len(kind)
+    arena = np.empty(n * bytes_per_record + 4096, np.uint8)
+    offsets = np.empty(3 * n + 1, np.uint64)
+    update_job = np.empty(n, np.uint32)
+    nbytes = C.c_uint64(0)
+    n_up = lib().nxo_encode_strings(_p(kind, C.c_uint8), _p(reason, C.c_uint16), _p(flags, C.c_uint8),
+                                    _p(stage, C.c_uint8), _p(key, C.c_uint64), n, finished_mask, arena.ctypes.data,
+                                    arena.nbytes, offsets.ctypes.data, update_job.ctypes.data, C.byref(nbytes))
+    assert n_up != 2**64 - 1, "arena too small"
+    return arena[:nbytes.value], offsets[:3 * n_up + 1], update_job[:n_up]
 
 
 def generate(workload, n, seed=0x6E65787573, first=0, shard=0, n_shards=1):

@@ -484,6 +484,49 @@ LoopResult event_loop(const Columns &c, const EventStrings *strs, uint64_t lo, u
 
 extern "C" {
 
+// String-mode replay that returns what the reference would have WRITTEN: for every job whose row was
+// upserted at least once, the three strings superviseAction set (lifecycle_stage,
+// algorithm_failure_cause, algorithm_failure_details), back to back in `arena`, offsets[3u..3u+3] per
+// updated job u, update_job[u] = index of the job in the stream.  event.Message of record i is the text
+// "m<i>".  Returns the number of updated jobs (UINT64_MAX when the arena is too small).
+uint64_t nxo_encode_strings(const uint8_t *kind, const uint16_t *reason, const uint8_t *flags, const uint8_t *stage,
+                            const uint64_t *key, uint64_t n, uint16_t finished_mask, uint8_t *arena, uint64_t cap,
+                            uint64_t *offsets, uint32_t *update_job, uint64_t *arena_bytes) {
+  uint64_t n_up = 0, pos = 0, job = 0;
+  Checkpoint row;
+  bool upserted = false;
+  char name_buf[40], msg_buf[32];
+  for (uint64_t i = 0; i < n; ++i) {
+    if (i == 0 || key[i] != key[i - 1]) {
+      row = Checkpoint{stage_name(stage[i]), "", ""};
+      upserted = false;
+    }
+    snprintf(name_buf, sizeof name_buf, "%016llx", (unsigned long long)key[i]);
+    snprintf(msg_buf, sizeof msg_buf, "m%llu", (unsigned long long)i);
+    const Event ev{kind[i] < 3 ? kKindNames[kind[i]] : "Other", reason[i] < 16 ? kReasonNames[reason[i]] : "Unknown",
+                   msg_buf, "uid", name_buf};
+    const CachedObject obj{(flags[i] & 2) != 0, name_buf, "test-algorithm"};
+    const auto res = on_event(ev, (flags[i] & 1) != 0, obj);
+    if (res) upserted |= supervise_action(*res, (flags[i] & 4) ? &row : nullptr, finished_mask).upsert;
+    if (i + 1 == n || key[i + 1] != key[i]) {
+      if (upserted) {
+        const std::string *parts[3] = {&row.lifecycle_stage, &row.failure_cause, &row.failure_details};
+        for (int k = 0; k < 3; ++k) {
+          if (pos + parts[k]->size() > cap) return UINT64_MAX;
+          offsets[3 * n_up + k] = pos;
+          memcpy(arena + pos, parts[k]->data(), parts[k]->size());
+          pos += parts[k]->size();
+        }
+        update_job[n_up++] = (uint32_t)job;
+      }
+      ++job;
+    }
+  }
+  offsets[3 * n_up] = pos;
+  *arena_bytes = pos;
+  return n_up;
+}
+
 // Best-of-`repeats` wall time of event_loop over the n records, split over `threads` ranges cut on job
 // boundaries; the per-record strings are materialised by each thread before the timed region.
 double nxo_bench_event_loop(int threads, const uint8_t *kind, const uint16_t *reason, const uint8_t *flags,
