@@ -100,6 +100,14 @@ def main():
             later = [np.median([x[2][j] - x[2][j - 1] for x in st if j in x[2] and j - 1 in x[2]]) for j in range(1, nj)]
             tail = np.median([x[1] - x[2][nj - 1] for x in st if x[1] and nj - 1 in x[2]])
             print(f" steps of warp 0 (ns): start->step0 {int(first)}  step j-1->j {[int(v) for v in later]}  last step->end {int(tail)}")
+        seq = sorted((per[(cta, t)]["p1_start"], per[(cta, t)].get("p1_end"), per[(cta, t)].get("issued"), t) for t in tiles
+                     if "p1_start" in per[(cta, t)])
+        gaps = [b[0] - a[1] for a, b in zip(seq, seq[1:]) if a[1]]
+        land = [x[0] - x[2] for x in seq if x[2]]
+        if gaps:
+            print(f" workers: end of a tile's passes -> start of the next record pass (ns, median / p90 / max): "
+                  f"{int(np.median(gaps))} / {int(np.percentile(gaps, 90))} / {int(max(gaps))};  bulk copies issued -> record pass "
+                  f"starts: {int(np.median(land))} / {int(np.percentile(land, 90))} / {int(max(land))}")
         if len(tiles) > 1:
             claims = np.array([per[(cta, t)]["claim"] for t in tiles if "claim" in per[(cta, t)]])
             print(f" tile period (claim to claim): median {int(np.median(np.diff(np.sort(claims))))} ns")
