@@ -50,7 +50,7 @@ constexpr int kWorkerWarps = NXS_WORKERS;
 constexpr int kWorkers = kWorkerWarps * 32;
 constexpr int kProducerWarp = kWorkerWarps;
 constexpr int kSummaryWarp = kWorkerWarps + 1;
-constexpr int kCounterWarp0 = kWorkerWarps + 2; // first of kCounterWarps counter warps
+constexpr int kCounterWarp0 = kWorkerWarps + 2; // first of the kCounterWarps look-back warps
 #ifndef NXS_COUNTER_WARPS
 #define NXS_COUNTER_WARPS 2
 #endif
@@ -174,7 +174,7 @@ template <int STAGES> struct Ctl {
 
 // Tile descriptor: two self-validating 64-bit words, each published with one
 // relaxed store, so no fence is needed on either side.
-//   c: job count[0,32) | status[32,34) | generation[34,41)      (counter warp)
+//   c: job count[0,32) | status[32,34) | generation[34,41)      (look-back warp)
 //   s: win_idx[0,32) | Summ.f[32,55) | status[55,57) | generation[57,64)   (summary warp)
 struct __align__(16) TileDesc {
   uint64_t c, s;
@@ -449,7 +449,7 @@ __device__ __forceinline__ void marker_loop(const ClassifyParams &p, StageBuf<TI
   }
 }
 
-// ----------------------------------------------------------------- counter warp
+// ----------------------------------------------------------------- look-back warps
 struct CountLookback {
   int pos;       // nearest predecessor tile of the next window
   uint32_t excl; // job rows counted so far

@@ -9,6 +9,7 @@
 // verdicts at the position of their record, job rows in the order in which the jobs end in the
 // stream.  No collective, no peer access: G independent H2D / kernel / D2H pipelines.
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -174,6 +175,14 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
   }
   const uint32_t G = h->n_shards;
   const uint64_t *key = in->job_key;
+  const bool verbose = getenv("NXS_VERBOSE") != nullptr;
+  auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  double t_mark = now();
+  auto lap = [&](const char *what) {
+    const double t = now();
+    if (verbose) fprintf(stderr, "nxs sharded: %-28s %8.1f ms\n", what, (t - t_mark) * 1e3);
+    t_mark = t;
+  };
 
   // ---- host chunks, cut on job boundaries, for the parallel partition and gather
   const uint64_t chunk_min = h->shard[0].pinned ? (1u << 16) : 64u; // (tiny chunks only under the CPU test hook)
@@ -195,7 +204,7 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
     for (std::thread &x : th) x.join();
   };
   parallel([&](unsigned t) {
-    uint64_t *rc = &rec_cnt[(size_t)t * G], *jc = &job_cnt[(size_t)t * G];
+    uint64_t rc[256] = {0}, jc[256] = {0}; // thread-local: neighbours' counters would share cache lines
     for (uint64_t i = cut[t]; i < cut[t + 1];) {
       const uint64_t k = key[i];
       uint64_t j = i + 1;
@@ -205,7 +214,9 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
       jc[s] += 1;
       i = j;
     }
+    for (uint32_t s = 0; s < G; ++s) rec_cnt[(size_t)t * G + s] = rc[s], job_cnt[(size_t)t * G + s] = jc[s];
   });
+  lap("count (records, jobs / shard)");
   // exclusive prefix over the chunks, per shard
   std::vector<uint64_t> rec_off((size_t)T * G), job_off((size_t)T * G), chunk_job0(T + 1, 0);
   for (uint32_t s = 0; s < G; ++s) {
@@ -231,6 +242,7 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
   }
   const uint64_t total_jobs = chunk_job0[T];
 
+  lap("prefix + staging buffers");
   // ---- partition: every shard's records in stream order
   parallel([&](unsigned t) {
     std::vector<uint64_t> w(rec_off.begin() + (size_t)t * G, rec_off.begin() + (size_t)(t + 1) * G);
@@ -241,18 +253,21 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
       ShardBuf &b = h->shard[nxs_shard_of(k, G)];
       uint64_t &pos = w[&b - h->shard.data()];
       const uint64_t m = j - i;
-      for (uint64_t q = 0; q < m; ++q) b.key[pos + q] = k;
-      memcpy(b.reason + pos, in->reason_id + i, m * 2);
-      memcpy(b.kind + pos, in->kind + i, m);
-      memcpy(b.flags + pos, in->flags + i, m);
-      memcpy(b.stage + pos, in->cur_stage + i, m);
-      for (uint64_t q = 0; q < m; ++q) b.idx[pos + q] = (uint32_t)(i + q);
+      for (uint64_t q = 0; q < m; ++q) { // (jobs are a few records long: plain loops beat four memcpy calls)
+        b.key[pos + q] = k;
+        b.reason[pos + q] = in->reason_id[i + q];
+        b.kind[pos + q] = in->kind[i + q];
+        b.flags[pos + q] = in->flags[i + q];
+        b.stage[pos + q] = in->cur_stage[i + q];
+        b.idx[pos + q] = (uint32_t)(i + q);
+      }
       pos += m;
       i = j;
     }
   });
 
-  // ---- classify: one thread per shard, each on its own ctx (and GPU), then scatter its verdicts
+  lap("partition (scatter)");
+  // ---- classify: one thread per shard, each on its own ctx (and GPU)
   {
     std::vector<std::thread> th;
     auto run = [&](uint32_t s) {
@@ -264,17 +279,13 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
       nxs_out sout{b.verdict, b.rows, &jobs};
       b.rc = classify(user, s, &sin, &sout);
       if (b.rc != NXS_OK) return;
-      if (jobs != b.n_jobs) {
-        b.rc = NXS_ERR_CUDA;
-        return;
-      }
-      uint32_t *v = out->verdict;
-      for (uint64_t q = 0; q < b.n; ++q) v[b.idx[q]] = b.verdict[q];
+      if (jobs != b.n_jobs) b.rc = NXS_ERR_CUDA;
     };
     for (uint32_t s = 1; s < G; ++s) th.emplace_back(run, s);
     run(0);
     for (std::thread &x : th) x.join();
   }
+  lap("classify (all shards)");
   for (uint32_t s = 0; s < G; ++s)
     if (h->shard[s].rc != NXS_OK) {
       snprintf(h->err, sizeof h->err, "shard %u on device %d: %s: %s", s, h->shard[s].device, nxs_strerror(h->shard[s].rc),
@@ -282,9 +293,17 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
       return h->shard[s].rc;
     }
 
-  // ---- gather the job rows: jobs in the order in which they end in the stream; a shard's rows are
-  // already in that order among themselves, so row j of the stream is the next unread row of its shard
+  // ---- gather.  Verdicts: the records of chunk t that went to shard s sit in one piece of the shard's
+  // buffers, with their stream positions beside them.  Job rows: jobs in the order in which they end in
+  // the stream; a shard's rows are already in that order among themselves, so row j of the stream is
+  // the next unread row of its shard.
   parallel([&](unsigned t) {
+    uint32_t *v = out->verdict;
+    for (uint32_t s = 0; s < G; ++s) {
+      const ShardBuf &b = h->shard[s];
+      const uint64_t lo = rec_off[(size_t)t * G + s], hi = lo + rec_cnt[(size_t)t * G + s];
+      for (uint64_t q = lo; q < hi; ++q) v[b.idx[q]] = b.verdict[q];
+    }
     std::vector<uint64_t> r(job_off.begin() + (size_t)t * G, job_off.begin() + (size_t)(t + 1) * G);
     nxs_job_row *dst = out->job_rows + chunk_job0[t];
     for (uint64_t i = cut[t]; i < cut[t + 1];) {
@@ -298,6 +317,7 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
       i = j;
     }
   });
+  lap("gather (verdicts, job rows)");
   *out->n_jobs = total_jobs;
   return NXS_OK;
 }
