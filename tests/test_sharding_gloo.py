@@ -109,8 +109,13 @@ def test_product_partition_and_gather_with_the_oracle_as_classifier(G):
         return 0
 
     rng = np.random.default_rng(G)
-    for n, max_len in ((1, 1), (777, 3), (40_000, 6), (30_001, 900)):
-        cols = util.random_cols(rng, n, max_len)
+    cases = [util.random_cols(rng, n, max_len) for n, max_len in ((1, 1), (777, 3), (40_000, 6), (30_001, 900))]
+    one_job = util.random_cols(rng, 5_000, 1, wide=False)
+    one_job["job_key"][:] = 99  # a single job: one shard gets everything, the others nothing
+    few = util.random_cols(rng, 3, 1)  # fewer records than shards
+    cases += [one_job, few]
+    for cols in cases:
+        n = len(cols["kind"])
         verdict = np.zeros(n, np.uint32)
         rows = np.zeros(n, cpu_oracle.JOB_ROW)
         nj = C.c_uint64(0)
