@@ -1,6 +1,7 @@
 // nxs_classify.cu — context, launch logic and the C ABI declared in
 // include/nxs_classify.h.  The GPU path is the only path: no CPU fallback.
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -451,6 +452,9 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
       return brc;
     }
   }
+  const bool verbose = (bounce_in || bounce_out) && getenv("NXS_VERBOSE") != nullptr;
+  double t_in = 0, t_out = 0, t_wait_count = 0, t_wait_d2h = 0;
+  auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
   uint64_t lo = 0, rows_done = 0;
   uint64_t pend_lo[2] = {0, 0}, pend_n[2] = {0, 0}; // slices whose rows are still to be downloaded
   bool pending[2] = {false, false};
@@ -459,7 +463,9 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
   uint64_t out_lo[2] = {0, 0}, out_n[2] = {0, 0}, out_row0[2] = {0, 0}, out_jobs[2] = {0, 0};
   int rc = NXS_OK;
   auto finish_slice = [&](int b) -> int { // job count is (about to be) on the host: download the rows
+    const double t0 = now();
     NXS_CUDA(ctx, cudaEventSynchronize(ctx->e_count[b]));
+    t_wait_count += now() - t0;
     const uint64_t jobs = ctx->h_njobs[b];
     if (jobs > pend_n[b]) {
       snprintf(ctx->err, sizeof ctx->err, "internal error: %llu jobs in a slice of %llu records",
@@ -477,12 +483,16 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
   };
   auto copy_out = [&](int b) -> int { // bounce buffers of set b -> the caller's buffers, once its downloads are done
     if (!out_wait[b]) return NXS_OK;
+    const double t0 = now();
     NXS_CUDA(ctx, cudaEventSynchronize(ctx->e_d2h[b]));
+    const double t1 = now();
+    t_wait_d2h += t1 - t0;
     CopySeg seg[2];
     int ns = 0;
     if (out->verdict) seg[ns++] = CopySeg{out->verdict + out_lo[b], ctx->h_verdict[b], out_n[b] * 4};
     seg[ns++] = CopySeg{out->job_rows + out_row0[b], ctx->h_rows[b], out_jobs[b] * sizeof(nxs_job_row)};
     par_copy(seg, ns);
+    t_out += now() - t1;
     out_wait[b] = false;
     return NXS_OK;
   };
@@ -519,7 +529,9 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
       uint8_t *hb = ctx->h_in[b];
       CopySeg seg[5] = {{hb, s_key, m * 8}, {hb + cap * 8, s_reason, m * 2}, {hb + cap * 10, s_kind, attr ? 0 : m},
                         {hb + cap * 11, s_flags, attr ? 0 : m}, {hb + cap * 12, s_stage, attr ? 0 : m}};
+      const double t0 = now();
       par_copy(seg, 5);
+      t_in += now() - t0;
       s_key = reinterpret_cast<const uint64_t *>(hb);
       s_reason = reinterpret_cast<const uint16_t *>(hb + cap * 8);
       s_kind = hb + cap * 10, s_flags = hb + cap * 11, s_stage = hb + cap * 12;
@@ -579,6 +591,9 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
   }
   NXS_CUDA(ctx, cudaStreamSynchronize(ctx->s_d2h));
   NXS_CUDA(ctx, cudaStreamSynchronize(s_comp));
+  if (verbose)
+    fprintf(stderr, "nxs bounce: copy in %.1f ms, copy out %.1f ms, waiting for job counts %.1f ms, for downloads %.1f ms\n",
+            t_in * 1e3, t_out * 1e3, t_wait_count * 1e3, t_wait_d2h * 1e3);
   *out->n_jobs = rows_done;
   return NXS_OK;
 }
