@@ -28,7 +28,6 @@ struct ShardBuf {
   uint64_t *key = nullptr;
   uint16_t *reason = nullptr;
   uint8_t *kind = nullptr, *flags = nullptr, *stage = nullptr;
-  uint32_t *idx = nullptr; // shard position -> stream position
   uint32_t *verdict = nullptr;
   nxs_job_row *rows = nullptr;
   uint64_t n = 0, n_jobs = 0;
@@ -51,20 +50,19 @@ void free_bufs(ShardBuf &b) {
   free_one(b, b.kind);
   free_one(b, b.flags);
   free_one(b, b.stage);
-  free_one(b, b.idx);
   free_one(b, b.verdict);
   free_one(b, b.rows);
   b.key = nullptr, b.reason = nullptr, b.kind = b.flags = b.stage = nullptr;
-  b.idx = b.verdict = nullptr, b.rows = nullptr, b.cap = 0;
+  b.verdict = nullptr, b.rows = nullptr, b.cap = 0;
 }
 
 int grow_bufs(ShardBuf &b, uint64_t want) {
   if (want <= b.cap) return NXS_OK;
   free_bufs(b);
   const uint64_t cap = (want + want / 16 + 4095) & ~4095ull;
-  void *p[8] = {nullptr};
-  const size_t bytes[8] = {cap * 8, cap * 2, cap, cap, cap, cap * 4, cap * 4, cap * sizeof(nxs_job_row)};
-  for (int i = 0; i < 8; ++i) {
+  void *p[7] = {nullptr};
+  const size_t bytes[7] = {cap * 8, cap * 2, cap, cap, cap, cap * 4, cap * sizeof(nxs_job_row)};
+  for (int i = 0; i < 7; ++i) {
     if (b.pinned) {
       if (nxs_alloc_host(bytes[i], &p[i]) != NXS_OK) p[i] = nullptr;
     } else {
@@ -77,8 +75,8 @@ int grow_bufs(ShardBuf &b, uint64_t want) {
   }
   b.key = static_cast<uint64_t *>(p[0]), b.reason = static_cast<uint16_t *>(p[1]);
   b.kind = static_cast<uint8_t *>(p[2]), b.flags = static_cast<uint8_t *>(p[3]), b.stage = static_cast<uint8_t *>(p[4]);
-  b.idx = static_cast<uint32_t *>(p[5]), b.verdict = static_cast<uint32_t *>(p[6]);
-  b.rows = static_cast<nxs_job_row *>(p[7]);
+  b.verdict = static_cast<uint32_t *>(p[5]);
+  b.rows = static_cast<nxs_job_row *>(p[6]);
   b.cap = cap;
   return NXS_OK;
 }
@@ -259,7 +257,6 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
         b.kind[pos + q] = in->kind[i + q];
         b.flags[pos + q] = in->flags[i + q];
         b.stage[pos + q] = in->cur_stage[i + q];
-        b.idx[pos + q] = (uint32_t)(i + q);
       }
       pos += m;
       i = j;
@@ -293,26 +290,26 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
       return h->shard[s].rc;
     }
 
-  // ---- gather.  Verdicts: the records of chunk t that went to shard s sit in one piece of the shard's
-  // buffers, with their stream positions beside them.  Job rows: jobs in the order in which they end in
-  // the stream; a shard's rows are already in that order among themselves, so row j of the stream is
-  // the next unread row of its shard.
+  // ---- gather: the stream is walked job by job once more.  A shard's records and job rows are in stream
+  // order among themselves, so the next job of the stream finds its verdicts and its row at the shard's
+  // cursors; its winner index is shard-local and moves with the job's first record.
   parallel([&](unsigned t) {
-    uint32_t *v = out->verdict;
-    for (uint32_t s = 0; s < G; ++s) {
-      const ShardBuf &b = h->shard[s];
-      const uint64_t lo = rec_off[(size_t)t * G + s], hi = lo + rec_cnt[(size_t)t * G + s];
-      for (uint64_t q = lo; q < hi; ++q) v[b.idx[q]] = b.verdict[q];
-    }
+    // cursors of this chunk in every shard's buffers: records and job rows
+    std::vector<uint64_t> rpos(rec_off.begin() + (size_t)t * G, rec_off.begin() + (size_t)(t + 1) * G);
     std::vector<uint64_t> r(job_off.begin() + (size_t)t * G, job_off.begin() + (size_t)(t + 1) * G);
+    uint32_t *v = out->verdict;
     nxs_job_row *dst = out->job_rows + chunk_job0[t];
     for (uint64_t i = cut[t]; i < cut[t + 1];) {
       const uint64_t k = key[i];
       uint64_t j = i + 1;
       while (j < cut[t + 1] && key[j] == k) ++j;
       const ShardBuf &b = h->shard[nxs_shard_of(k, G)];
-      nxs_job_row row = b.rows[r[&b - h->shard.data()]++];
-      if (row.winner_idx != NXS_NO_WINNER) row.winner_idx = b.idx[row.winner_idx];
+      const size_t s = &b - h->shard.data();
+      const uint64_t p0 = rpos[s]; // the job's records sit at [p0, p0 + j - i) of its shard, in stream order
+      for (uint64_t q = 0; q < j - i; ++q) v[i + q] = b.verdict[p0 + q];
+      rpos[s] = p0 + (j - i);
+      nxs_job_row row = b.rows[r[s]++];
+      if (row.winner_idx != NXS_NO_WINNER) row.winner_idx = (uint32_t)(i + (row.winner_idx - p0)); // shard -> stream index
       *dst++ = row;
       i = j;
     }
