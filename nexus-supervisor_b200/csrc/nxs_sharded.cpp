@@ -81,6 +81,28 @@ int grow_bufs(ShardBuf &b, uint64_t want) {
   return NXS_OK;
 }
 
+// nxs_shard_of(key, G) = splitmix64(key) % G for every record of a pass, without a division: G a power
+// of two is a mask; otherwise the 64-bit hash is folded as (hi * (2^32 mod G) + lo) mod G with the exact
+// 32-bit remainder-by-multiplication (a mod d = ((M * a mod 2^64) * d) >> 64 with M = floor((2^64 - 1) / d) + 1,
+// exact for every 32-bit a and d; D. Lemire, O. Kaser, N. Kurz, "Faster remainder by direct computation", 2019).
+struct ShardMap {
+  uint64_t M = 0;
+  uint32_t d = 1, c = 0, mask = 0;
+  bool pow2 = true;
+  explicit ShardMap(uint32_t G) : d(G ? G : 1) {
+    pow2 = (d & (d - 1)) == 0;
+    mask = d - 1;
+    M = ~0ull / d + 1;
+    c = (uint32_t)((1ull << 32) % d);
+  }
+  inline uint32_t mod32(uint32_t a) const { return (uint32_t)(((unsigned __int128)(M * a) * d) >> 64); }
+  inline uint32_t operator()(uint64_t key) const {
+    const uint64_t h = nxs::splitmix64(key);
+    if (pow2) return (uint32_t)h & mask;
+    return mod32(mod32((uint32_t)(h >> 32)) * c + mod32((uint32_t)h));
+  }
+};
+
 } // namespace
 
 struct nxs_sharded {
@@ -153,6 +175,7 @@ int nxs_internal_sharded_run(uint32_t n_shards, const nxs_batch *in, const nxs_o
   h.shard.resize(n_shards);
   for (ShardBuf &b : h.shard) b.pinned = false;
   h.host_threads = 3; // more chunks than one, fewer than the shards of some tests
+  if (const char *e = getenv("NXS_HOOK_THREADS")) h.host_threads = (unsigned)std::max(1, atoi(e)); // (host-pass timing)
   const int rc = classify_sharded_impl(&h, in, out, classify, user);
   for (ShardBuf &b : h.shard) free_bufs(b);
   return rc;
@@ -201,16 +224,19 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
     fn(0u);
     for (std::thread &x : th) x.join();
   };
+  // The three host passes below visit RECORDS, not jobs: a loop over the few records of a job ends on a
+  // branch nobody can predict, and at a few records per job that branch was most of the time.  The shard
+  // is recomputed for every record (a hash and a mask or three multiplications), cursors advance by 0 or 1.
+  const ShardMap shard_of(G);
   parallel([&](unsigned t) {
     uint64_t rc[256] = {0}, jc[256] = {0}; // thread-local: neighbours' counters would share cache lines
-    for (uint64_t i = cut[t]; i < cut[t + 1];) {
+    uint64_t prev = ~key[cut[t]];          // (differs from the chunk's first key: the first record begins a job)
+    for (uint64_t i = cut[t]; i < cut[t + 1]; ++i) {
       const uint64_t k = key[i];
-      uint64_t j = i + 1;
-      while (j < cut[t + 1] && key[j] == k) ++j;
-      const uint32_t s = nxs_shard_of(k, G);
-      rc[s] += j - i;
-      jc[s] += 1;
-      i = j;
+      const uint32_t s = shard_of(k);
+      rc[s] += 1;
+      jc[s] += k != prev;
+      prev = k;
     }
     for (uint32_t s = 0; s < G; ++s) rec_cnt[(size_t)t * G + s] = rc[s], job_cnt[(size_t)t * G + s] = jc[s];
   });
@@ -242,24 +268,31 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
 
   lap("prefix + staging buffers");
   // ---- partition: every shard's records in stream order
+  struct Cols { // a shard's staging columns (local copies: the byte stores below may alias anything else)
+    uint64_t *key;
+    uint16_t *reason;
+    uint8_t *kind, *flags, *stage;
+  };
   parallel([&](unsigned t) {
-    std::vector<uint64_t> w(rec_off.begin() + (size_t)t * G, rec_off.begin() + (size_t)(t + 1) * G);
-    for (uint64_t i = cut[t]; i < cut[t + 1];) {
+    uint64_t w[256];
+    Cols d[256];
+    for (uint32_t s = 0; s < G; ++s) {
+      const ShardBuf &b = h->shard[s];
+      w[s] = rec_off[(size_t)t * G + s];
+      d[s] = Cols{b.key, b.reason, b.kind, b.flags, b.stage};
+    }
+    const uint16_t *reason = in->reason_id;
+    const uint8_t *kind = in->kind, *flags = in->flags, *stage = in->cur_stage;
+    for (uint64_t i = cut[t]; i < cut[t + 1]; ++i) {
       const uint64_t k = key[i];
-      uint64_t j = i + 1;
-      while (j < cut[t + 1] && key[j] == k) ++j;
-      ShardBuf &b = h->shard[nxs_shard_of(k, G)];
-      uint64_t &pos = w[&b - h->shard.data()];
-      const uint64_t m = j - i;
-      for (uint64_t q = 0; q < m; ++q) { // (jobs are a few records long: plain loops beat four memcpy calls)
-        b.key[pos + q] = k;
-        b.reason[pos + q] = in->reason_id[i + q];
-        b.kind[pos + q] = in->kind[i + q];
-        b.flags[pos + q] = in->flags[i + q];
-        b.stage[pos + q] = in->cur_stage[i + q];
-      }
-      pos += m;
-      i = j;
+      const uint32_t s = shard_of(k);
+      const uint64_t pos = w[s]++;
+      const Cols &c = d[s];
+      c.key[pos] = k;
+      c.reason[pos] = reason[i];
+      c.kind[pos] = kind[i];
+      c.flags[pos] = flags[i];
+      c.stage[pos] = stage[i];
     }
   });
 
@@ -290,29 +323,43 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
       return h->shard[s].rc;
     }
 
-  // ---- gather: the stream is walked job by job once more.  A shard's records and job rows are in stream
-  // order among themselves, so the next job of the stream finds its verdicts and its row at the shard's
-  // cursors; its winner index is shard-local and moves with the job's first record.
+  // ---- gather: the stream is walked once more.  A shard's records and job rows are in stream order among
+  // themselves, so every record finds its verdict, and the last record of a job the job's row, at the
+  // shard's cursors; a winner index is shard-local and moves with the job's first record.  The row is
+  // written for every record of a job and the output cursor advances only behind the last one (a chunk
+  // ends on a job boundary, so every such early write is overwritten from inside the chunk).
   parallel([&](unsigned t) {
-    // cursors of this chunk in every shard's buffers: records and job rows
-    std::vector<uint64_t> rpos(rec_off.begin() + (size_t)t * G, rec_off.begin() + (size_t)(t + 1) * G);
-    std::vector<uint64_t> r(job_off.begin() + (size_t)t * G, job_off.begin() + (size_t)(t + 1) * G);
+    uint64_t rpos[256], r[256]; // this chunk's cursors in every shard's buffers: records and job rows
+    const uint32_t *sv[256];
+    const nxs_job_row *sr[256];
+    for (uint32_t s = 0; s < G; ++s) {
+      rpos[s] = rec_off[(size_t)t * G + s];
+      r[s] = job_off[(size_t)t * G + s];
+      sv[s] = h->shard[s].verdict;
+      sr[s] = h->shard[s].rows;
+    }
     uint32_t *v = out->verdict;
     nxs_job_row *dst = out->job_rows + chunk_job0[t];
-    for (uint64_t i = cut[t]; i < cut[t + 1];) {
-      const uint64_t k = key[i];
-      uint64_t j = i + 1;
-      while (j < cut[t + 1] && key[j] == k) ++j;
-      const ShardBuf &b = h->shard[nxs_shard_of(k, G)];
-      const size_t s = &b - h->shard.data();
-      const uint64_t p0 = rpos[s]; // the job's records sit at [p0, p0 + j - i) of its shard, in stream order
-      for (uint64_t q = 0; q < j - i; ++q) v[i + q] = b.verdict[p0 + q];
-      rpos[s] = p0 + (j - i);
-      nxs_job_row row = b.rows[r[s]++];
-      if (row.winner_idx != NXS_NO_WINNER) row.winner_idx = (uint32_t)(i + (row.winner_idx - p0)); // shard -> stream index
-      *dst++ = row;
-      i = j;
-    }
+    const uint64_t lo = cut[t], hi = cut[t + 1];
+    if (lo == hi) return;
+    uint64_t prev = ~key[lo], first_i = lo, p0 = 0;
+    auto one = [&](uint64_t i, uint64_t k, bool tail) {
+      const uint32_t s = shard_of(k);
+      const uint64_t p = rpos[s]++;
+      v[i] = sv[s][p];
+      const bool head = k != prev;
+      first_i = head ? i : first_i; // where the job begins: in the stream, and in its shard
+      p0 = head ? p : p0;
+      prev = k;
+      nxs_job_row row = sr[s][r[s]];
+      r[s] += tail;
+      const uint32_t moved = (uint32_t)(first_i + (row.winner_idx - p0)); // shard -> stream index
+      row.winner_idx = row.winner_idx != NXS_NO_WINNER ? moved : row.winner_idx;
+      *dst = row;
+      dst += tail;
+    };
+    for (uint64_t i = lo; i + 1 < hi; ++i) one(i, key[i], key[i + 1] != key[i]);
+    one(hi - 1, key[hi - 1], true);
   });
   lap("gather (verdicts, job rows)");
   *out->n_jobs = total_jobs;
