@@ -163,6 +163,13 @@ int nxs_classify_sharded(nxs_sharded *h, const nxs_batch *in, const nxs_out *out
   return classify_sharded_impl(h, in, out, classify_on_ctx, h);
 }
 
+// Test hook (not in the public header): the division-free shard map of the host passes, to be compared
+// with nxs_shard_of.
+void nxs_internal_shard_map(const uint64_t *keys, uint64_t n, uint32_t n_shards, uint32_t *out) {
+  const ShardMap map(n_shards);
+  for (uint64_t i = 0; i < n; ++i) out[i] = map(keys[i]);
+}
+
 // Test hook (not in the public header): the partition and gather of nxs_classify_sharded around a
 // caller-supplied per-shard classifier, without any GPU — `pytest -m "not gpu"` runs the product's
 // host logic with the oracle standing in for the kernel.

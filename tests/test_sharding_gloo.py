@@ -77,6 +77,31 @@ def test_partition_keeps_jobs_whole_and_ordered():
     assert sizes.max() / sizes.mean() < 1.05
 
 
+def test_division_free_shard_map_equals_shard_of():
+    """The host passes of nxs_classify_sharded compute splitmix64(key) % G without a division (mask, or a
+    folded remainder by multiplication): same value as nxs_shard_of for every G the entry point accepts."""
+    import ctypes as C
+    import nexus_supervisor_b200 as nx
+    lib = nx._abi.load()
+    lib.nxs_internal_shard_map.restype = None
+    lib.nxs_internal_shard_map.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p]
+    rng = np.random.default_rng(5)
+    keys = rng.integers(0, 2**64, 4096, dtype=np.uint64)
+    keys[:8] = [0, 1, 2**32 - 1, 2**32, 2**63, 2**64 - 1, 0x6E65787573, 12345]
+    got = np.empty(len(keys), np.uint32)
+    for G in range(1, 257):
+        lib.nxs_internal_shard_map(keys.ctypes.data, len(keys), G, got.ctypes.data)
+        want = np.array([nx.shard_of(int(k), G) for k in keys[:64]], np.uint32)
+        assert np.array_equal(got[:64], want), G
+        # and the whole array against the definition, vectorised (splitmix64 in numpy)
+        with np.errstate(over="ignore"):
+            z = keys + np.uint64(0x9E3779B97F4A7C15)
+            z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+            z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+            z = z ^ (z >> np.uint64(31))
+        assert np.array_equal(got, (z % np.uint64(G)).astype(np.uint32)), G
+
+
 @pytest.mark.parametrize("G", [1, 2, 3, 8])
 def test_product_partition_and_gather_with_the_oracle_as_classifier(G):
     """The host logic of nxs_classify_sharded itself (C++: parallel partition on job boundaries, per-shard
