@@ -400,7 +400,7 @@ __device__ __forceinline__ void mark_range(const ClassifyParams &p, TileMeta<TIL
   const uint32_t g0 = tile * TILE + range * RANGE; // first record of the range
   const uint64_t *const key = p.key + g0 + lane;
   uint32_t jobs = 0;
-  if (g0 + RANGE < p.n) { // the range and the record behind it exist
+  if (g0 < p.n && p.n - g0 > RANGE) { // the range and the record behind it exist (no sum: g0 + RANGE may wrap at 2^32)
 #pragma unroll
     for (uint32_t j = 0; j < CPW; ++j) {
       const bool tail = __ldg(key + j * 32) != __ldg(key + j * 32 + 1);

@@ -301,6 +301,94 @@ def test_device_path_1e9_records_bit_exact():
     _full_size_check(1_000_000_000)
 
 
+@pytest.mark.skipif(os.environ.get("NXS_TEST_MAX", "1") == "0", reason="NXS_TEST_MAX=0")
+def test_device_path_maximum_batch_size():
+    """The largest batch the ABI takes — 2^32 - 2 records (winner indices are u32 and 0xFFFFFFFF means
+    "none") — in ONE launch: 524 288 tiles, 56 GB of columns.  Checked everywhere: the job count and every
+    row's key against the keys, every per-record verdict against a table built by the oracle over the whole
+    input domain; and bit for bit against the oracle (verdicts and job rows, winner indices included) on
+    windows at the start, across record 2^31 and at the very end of the batch."""
+    import torch
+    n = 2**32 - 2
+    free, _ = torch.cuda.mem_get_info()
+    if free < 150 * (1 << 30):
+        pytest.skip("needs 150 GB of free device memory")
+    step = 1 << 28
+    with nx.Classifier(device=0, max_records=n) as clf:
+        clf.set_stream(torch.cuda.current_stream().cuda_stream)
+        raw, ptr, cap = _device_columns(torch, n)
+        assert clf.generate_device(nx.WORKLOAD_SKEWED, n, ptr["kind"], ptr["reason_id"], ptr["flags"],
+                                   ptr["cur_stage"], ptr["job_key"], cap) == n
+        keys = raw[:cap * 8].view(torch.int64)[:n]
+
+        def tails_of(lo, hi):  # which records of [lo, hi) end a job
+            t = torch.ones(hi - lo, dtype=torch.bool, device="cuda")
+            last = min(hi, n - 1)
+            t[:last - lo] = keys[lo + 1:last + 1] != keys[lo:last]
+            return t
+        jobs_before = [0]  # job ends before record k * step
+        for lo in range(0, n, step):
+            jobs_before.append(jobs_before[-1] + int(tails_of(lo, min(n, lo + step)).sum().item()))
+        want_jobs = jobs_before[-1]
+        verdict = torch.empty(n, dtype=torch.int32, device="cuda")
+        rows = torch.empty((want_jobs + 1024, 2), dtype=torch.int64, device="cuda")
+        n_jobs = torch.zeros(1, dtype=torch.int64, device="cuda")
+        clf.classify_device(n, ptr["kind"], ptr["reason_id"], ptr["flags"], ptr["cur_stage"], ptr["job_key"],
+                            verdict.data_ptr(), rows.data_ptr(), n_jobs.data_ptr())
+        torch.cuda.synchronize()
+        assert clf.last_tile == 8192
+        assert int(n_jobs.item()) == want_jobs
+
+        # ---- everywhere: row keys, and the per-record verdicts against the oracle's table of the whole domain
+        K, R, F, S = 4, 64, 8, 16
+        dom = np.indices((K, R, F, S)).reshape(4, -1)
+        table_cols = {"kind": dom[0].astype(np.uint8), "reason_id": dom[1].astype(np.uint16), "flags": dom[2].astype(np.uint8),
+                      "cur_stage": dom[3].astype(np.uint8), "job_key": np.arange(dom.shape[1], dtype=np.uint64)}
+        table = torch.from_numpy(cpu_oracle.classify(table_cols)[0].view(np.int32)).cuda()
+        col = {name: raw[ptr[name] - ptr["job_key"]: ptr[name] - ptr["job_key"] + n * w]
+               for name, w in (("reason_id", 2), ("kind", 1), ("flags", 1), ("cur_stage", 1))}
+        reason_all = col["reason_id"].view(torch.int16)
+        for k, lo in enumerate(range(0, n, step)):
+            hi = min(n, lo + step)
+            t = tails_of(lo, hi)
+            assert torch.equal(rows[jobs_before[k]:jobs_before[k + 1], 0], keys[lo:hi][t]), f"row keys of records [{lo},{hi})"
+            del t
+            kind, reason = col["kind"][lo:hi].long(), reason_all[lo:hi].long()
+            flags, stage = col["flags"][lo:hi].long(), col["cur_stage"][lo:hi].long()
+            assert int(kind.max()) < K and int(reason.max()) < R and int(reason.min()) >= 0
+            assert int(flags.max()) < F and int(stage.max()) < S
+            idx = ((kind * R + reason) * F + flags) * S + stage
+            del kind, reason, flags, stage
+            assert torch.equal(verdict[lo:hi], table[idx]), f"per-record verdicts of [{lo},{hi})"
+            del idx
+
+        # ---- windows against the oracle, verdicts and rows bit for bit
+        threads = cpu_oracle.hardware_threads()
+        w = 4_000_000
+        for start in (0, 2**31 - w // 2, n - w):
+            lo = start
+            while lo > 0 and int(keys[lo].item()) == int(keys[lo - 1].item()):
+                lo += 1  # begin on a job boundary
+            hi = min(n, lo + w)
+            cols = cpu_oracle.generate(nx.WORKLOAD_SKEWED, hi - lo + 64, first=lo)
+            if hi < n:
+                k = cols["job_key"]
+                while k[hi - lo] == k[hi - lo - 1]:
+                    hi += 1
+            cols = {name: v[:hi - lo] for name, v in cols.items()}
+            assert np.array_equal(keys[lo:hi].cpu().numpy().view(np.uint64), cols["job_key"])
+            want_v, want_r = cpu_oracle.classify(cols, threads=threads)
+            want_r = want_r.copy()
+            has_w = want_r["winner_idx"] != nx.NO_WINNER
+            want_r["winner_idx"][has_w] += np.uint32(lo)
+            base = lo // step
+            row_lo = jobs_before[base] + int(tails_of(base * step, lo).sum().item()) if lo > base * step else jobs_before[base]
+            got_v = verdict[lo:hi].cpu().numpy().view(np.uint32)
+            got_r = rows[row_lo:row_lo + len(want_r)].cpu().numpy().view(np.uint64).reshape(-1, 2)
+            util.assert_same(got_v, got_r.copy().view(cpu_oracle.JOB_ROW).reshape(-1), want_v, want_r,
+                             f"records [{lo},{hi})")
+
+
 def _full_size_check(n):
     import torch
     with nx.Classifier(device=0, max_records=n) as clf:
