@@ -294,7 +294,10 @@ def test_device_path_full_size_bit_exact():
 def test_device_path_1e9_records_bit_exact():
     """The north-star size: 1e9 skewed records in ONE launch on one GPU (33 GB of columns, verdicts and
     rows), every verdict and job row compared with the oracle."""
+    import gc
     import torch
+    gc.collect()
+    torch.cuda.empty_cache()
     free, _ = torch.cuda.mem_get_info()
     if free < 80 * (1 << 30):
         pytest.skip("needs 80 GB of free device memory")
@@ -310,6 +313,9 @@ def test_device_path_maximum_batch_size():
     windows at the start, across record 2^31 and at the very end of the batch."""
     import torch
     n = 2**32 - 2
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()  # (what earlier tests left in torch's cache counts as used)
     free, _ = torch.cuda.mem_get_info()
     if free < 150 * (1 << 30):
         pytest.skip("needs 150 GB of free device memory")
