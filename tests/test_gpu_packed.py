@@ -60,3 +60,38 @@ def test_rows_only_device_path():
         jobs = int(nj.item())
         got = rows[:jobs].cpu().numpy().view(np.uint64).reshape(-1, 2).copy().view(cpu_oracle.JOB_ROW).reshape(-1)
         assert np.array_equal(got, want_r)
+
+
+def test_page_locked_caller_buffers_sliced():
+    """The fast host path: the caller's columns and outputs are page-locked (torch pinned memory here, what
+    nxs_alloc_host hands out), so the library copies straight from and to them, slice by slice, with no
+    bounce buffers in between — default call, rows only, and packed."""
+    import torch
+    rng = np.random.default_rng(47)
+    n = 19_000_017
+    cols = util.random_cols(rng, n, 9)
+    want_v, want_r = cpu_oracle.classify(cols, threads=cpu_oracle.hardware_threads())
+
+    def pin(a):
+        t = torch.from_numpy(a.view(np.uint8).reshape(-1).copy()).pin_memory()
+        assert t.is_pinned()
+        return t.numpy().view(a.dtype).reshape(a.shape), t  # (the tensor keeps the memory alive)
+    held = []
+    pinned = {}
+    for k, v in cols.items():
+        pinned[k], t = pin(v)
+        held.append(t)
+    out_v, tv = pin(np.full(n, 0xDEADBEEF, np.uint32))
+    out_r, tr = pin(np.zeros(n, cpu_oracle.JOB_ROW))
+    attr, ta = pin(nx.pack_columns(cols))
+    held += [tv, tr, ta]
+    with nx.Classifier(device=0, max_records=n) as c:
+        v, r = c.classify(pinned, out_verdict=out_v, out_rows=out_r)
+        util.assert_same(v, r, want_v, want_r, "page-locked buffers, sliced")
+        out_r[:] = np.zeros(1, cpu_oracle.JOB_ROW)
+        _, r2 = c.classify(pinned, out_rows=out_r, want_verdict=False)
+        assert np.array_equal(r2, want_r)
+        out_r[:] = np.zeros(1, cpu_oracle.JOB_ROW)
+        out_v[:] = 0
+        v3, r3 = c.classify_packed(pinned["job_key"], attr, out_verdict=out_v, out_rows=out_r, want_verdict=True)
+        util.assert_same(v3, r3, want_v, want_r, "page-locked buffers, packed")
