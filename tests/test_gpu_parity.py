@@ -113,6 +113,19 @@ def test_soak_many_launches_random_sizes(clf):
         util.assert_same(*clf.classify(cols), *cpu_oracle.classify(cols), f"soak launch {k} n={n} max_len={max_len}")
 
 
+def test_descriptor_generation_wraps():
+    """Tile descriptors carry a 7-bit launch generation instead of being cleared before every launch; after
+    127 launches of one context the scratch is zeroed and the count starts over.  300 launches of changing
+    size on one context: descriptors of every earlier generation lie around while each launch runs."""
+    rng = np.random.default_rng(127)
+    with nx.Classifier(device=0, max_records=400_000) as c:
+        for k in range(300):
+            n = int(rng.integers(1, 400_000)) if k % 3 else int(rng.integers(1, 20_000))
+            cols = util.random_cols(rng, n, (1, 3, 40, 3000)[k % 4])
+            util.assert_same(*c.classify(cols), *cpu_oracle.classify(cols), f"launch {k} n={n}")
+        assert c.launches == 300
+
+
 def test_host_path_slices_on_job_boundaries():
     """The host-pointer entry point processes large batches in ~8M-record slices (upload, classify and
     download overlapped); slices are cut on job boundaries and winner indices stay batch-relative."""
@@ -393,6 +406,32 @@ def test_device_path_maximum_batch_size():
             got_r = rows[row_lo:row_lo + len(want_r)].cpu().numpy().view(np.uint64).reshape(-1, 2)
             util.assert_same(got_v, got_r.copy().view(cpu_oracle.JOB_ROW).reshape(-1), want_v, want_r,
                              f"records [{lo},{hi})")
+
+
+def test_one_job_spanning_1e8_records():
+    """A batch that is ONE job (every tile but the last is head-less and tail-less: 12 208 tiles whose row
+    can only be closed through the look-back over summaries), and the same records cut into three jobs of
+    which the middle one spans 12 000 tiles."""
+    import torch
+    n = 100_000_000
+    with nx.Classifier(device=0, max_records=n) as clf:
+        clf.set_stream(torch.cuda.current_stream().cuda_stream)
+        raw, ptr, cap = _device_columns(torch, n)
+        assert clf.generate_device(nx.WORKLOAD_SKEWED, n, ptr["kind"], ptr["reason_id"], ptr["flags"],
+                                   ptr["cur_stage"], ptr["job_key"], cap) == n
+        cols = cpu_oracle.generate(nx.WORKLOAD_SKEWED, n)
+        keys = raw[:cap * 8].view(torch.int64)[:n]
+        for cuts in ((), (1_000_003, 99_304_999)):
+            key_host = np.full(n, 7, np.uint64)
+            for j, c in enumerate(cuts):
+                key_host[c:] = 8 + j
+            cols["job_key"] = key_host
+            keys.copy_(torch.from_numpy(key_host.view(np.int64)))
+            verdict, rows, n_jobs = _classify_device_full(torch, clf, ptr, n)
+            assert n_jobs == len(cuts) + 1
+            want_v, want_r = cpu_oracle.classify(cols, threads=1)
+            got_r = rows[:n_jobs].cpu().numpy().view(np.uint64).reshape(-1, 2).copy().view(cpu_oracle.JOB_ROW).reshape(-1)
+            util.assert_same(verdict.cpu().numpy().view(np.uint32), got_r, want_v, want_r, f"cuts={cuts}")
 
 
 def _full_size_check(n):
