@@ -139,6 +139,21 @@ def test_host_path_slices_on_job_boundaries():
         assert c.launches == 2 * 3
 
 
+@pytest.mark.parametrize("n", [(8 << 20) - 1, 8 << 20, (8 << 20) + 1, (9 << 20), (9 << 20) + 1, (16 << 20) + 5])
+def test_host_path_sizes_around_the_slice_cuts(n):
+    """Batches whose size sits on the edges of the slicing rule (one slice of up to 9 Mi records, otherwise
+    8 Mi-record slices and a last one of up to 9 Mi), with a job lying across every nominal cut."""
+    rng = np.random.default_rng(n & 0xFFFF)
+    cols = util.random_cols(rng, n, 3, wide=False)
+    for cut in range(8 << 20, n, 8 << 20):
+        cols["job_key"][cut - 700:min(n, cut + 900)] = np.uint64(0xC0FFEE00 + cut)
+    want = cpu_oracle.classify(cols, threads=cpu_oracle.hardware_threads())
+    with nx.Classifier(device=0, max_records=n) as c:
+        util.assert_same(*c.classify(cols), *want, f"n={n}")
+        _, rows = c.classify(cols, want_verdict=False)
+        assert np.array_equal(rows, want[1])
+
+
 def test_host_path_error_after_enqueued_slices_leaves_nothing_in_flight():
     """A job of four million records straddling a slice cut makes nxs_classify give up with
     NXS_ERR_CAPACITY after earlier slices have been uploaded, classified and queued for download.  The call
