@@ -1,8 +1,9 @@
 """GPU test of nxs_classify_device_noalloc, the entry point for hosts that cannot let the library
 allocate device memory (their own pool owns the HBM budget, or a cudaMalloc/cudaFree stall is not
 acceptable on their loop).  It keeps the kernel's scratch in a static __device__ array, so every call
-shares that array and must clear what it uses.  The test drives it through the C ABI twice in a row —
-a large batch, then a smaller, different one, so stale descriptors of the first call would show — and
+shares that array and must clear what it uses.  The test drives it through the C ABI several times in a row —
+a large batch, then a smaller, different one, so stale descriptors of the first call would show, then the
+largest batch it accepts — and
 requires bit-identical output to the ordinary entry point (nxs_classify_device) AND to the CPU oracle run
 on the same columns, an unchanged amount of free device memory across the second call, and a clean
 refusal above NXS_NOALLOC_MAX_RECORDS.
@@ -41,8 +42,10 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row():
     lib = nx._abi.load()
     stream = torch.cuda.current_stream().cuda_stream
     rng = np.random.default_rng(2024)
-    cases = [(3_000_001, 7, util.FM_DEFAULT, True), (70_003, 900, 0x5A5A, False)]
-    with nx.Classifier(device=0, max_records=1 << 22) as plain, \
+    # (the third batch is the largest the entry point takes: its last tile uses the last descriptor of the static scratch)
+    cases = [(3_000_001, 7, util.FM_DEFAULT, True), (70_003, 900, 0x5A5A, False),
+             (nx._abi.NXS_NOALLOC_MAX_RECORDS, 4, util.FM_DEFAULT, False)]
+    with nx.Classifier(device=0, max_records=1 << 24) as plain, \
             nx.Classifier(device=0, max_records=1 << 22, finished_mask=0x5A5A) as masked:
         for call, (n, max_len, fm, wide) in enumerate(cases):
             cols = util.random_cols(rng, n, max_len, wide=wide)
