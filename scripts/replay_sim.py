@@ -106,7 +106,7 @@ def pipeline_stream(records):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("bench", nargs="?", default=os.path.join(ROOT, "profiles", "r02_v11_bench.json"))
+    ap.add_argument("bench", nargs="?", default=os.path.join(ROOT, "profiles", "r02_final_bench.json"))
     ap.add_argument("--records", type=int, default=10_000_000, help="records of the stream run through the pipeline")
     ap.add_argument("--sim-elements", type=int, default=20_000, help="elements simulated in detail per sink")
     args = ap.parse_args()
