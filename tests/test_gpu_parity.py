@@ -74,6 +74,40 @@ def test_jobs_straddling_warps_tiles_and_ctas(clf, max_len):
             util.assert_same(*c.classify(cols), *cpu_oracle.classify(cols, fm), f"max_len={max_len} fm={fm:#x}")
 
 
+@pytest.mark.parametrize("length", [31, 32, 33, 63, 64, 65, 511, 512, 513, 8191, 8192, 8193])
+def test_jobs_of_exact_boundary_lengths(clf, length):
+    """Jobs whose length is exactly a chunk (32), a worker range (512) or a tile (8192), one less and one
+    more, at every alignment: the stream starts with a job of 0..length-1 records, and a few single-record
+    jobs are sprinkled in so that the alignment drifts.  Dense and sparse records (mostly handled failures,
+    mostly ignored events) so that stops fall on the first, the last and no record of a run."""
+    rng = np.random.default_rng(length)
+    n = 600_000 if length < 1000 else 1_500_000
+    for dense in (True, False):
+        for lead in (0, 1, length // 2, length - 1):
+            lens = [lead] if lead else []
+            while sum(lens) < n:
+                lens.append(length)
+                if rng.random() < 0.05:
+                    lens.append(1)
+            lens = np.array(lens)
+            with np.errstate(over="ignore"):
+                ids = np.arange(1, len(lens) + 1, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15)
+            keys = np.repeat(ids, lens)[:n]
+            if dense:
+                kind, reason = rng.integers(1, 3, n), rng.integers(1, 8, n)
+            else:
+                kind = rng.integers(1, 3, n)
+                reason = np.where(rng.random(n) < 0.002, rng.integers(1, 8, n), 9)
+            stage = np.repeat(rng.integers(1, 3, len(lens)), lens)[:n]
+            cols = util.make_cols(kind, reason, np.full(n, 7), stage, keys)
+            for fm in (util.FM_DEFAULT, 0):
+                if fm == util.FM_DEFAULT:
+                    util.assert_same(*clf.classify(cols), *cpu_oracle.classify(cols), f"length={length} lead={lead} dense={dense}")
+                else:
+                    with nx.Classifier(device=0, max_records=n, finished_mask=0) as c:
+                        util.assert_same(*c.classify(cols), *cpu_oracle.classify(cols, 0), f"length={length} lead={lead} dense={dense} fm=0")
+
+
 def test_single_job_batch(clf):
     n = 300_000
     rng = np.random.default_rng(3)
