@@ -237,7 +237,8 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
   const ShardMap shard_of(G);
   parallel([&](unsigned t) {
     uint64_t rc[256] = {0}, jc[256] = {0}; // thread-local: neighbours' counters would share cache lines
-    uint64_t prev = ~key[cut[t]];          // (differs from the chunk's first key: the first record begins a job)
+    // (prev differs from the chunk's first key: the first record begins a job; an empty chunk reads nothing)
+    uint64_t prev = cut[t] < cut[t + 1] ? ~key[cut[t]] : 0;
     for (uint64_t i = cut[t]; i < cut[t + 1]; ++i) {
       const uint64_t k = key[i];
       const uint32_t s = shard_of(k);
