@@ -272,6 +272,17 @@ const char *nxs_msg_template(uint32_t idx);
 /* AlgorithmFailureCause formats (:298,:325,:350); idx 0 = NULL (untouched) */
 const char *nxs_cause_template(uint32_t idx);
 
+/* EXTENSION — no counterpart in the reference, no parity claimed.  The reference classifies Kubernetes
+ * Events; container-status reasons (OOMKilled, ImagePullBackOff, ...) never reach it as such.  For
+ * streams phrased in that vocabulary this names the EVENT through which kubelet / the job controller
+ * surface such a status (outside the reference): OOMKilled -> Job / PodFailurePolicy (exit 137 matching
+ * the Job's podFailurePolicy: the reference's own comment, services/supervisor.go:311-312),
+ * ImagePullBackOff and CrashLoopBackOff -> Pod / BackOff, ErrImagePull -> Pod / Failed.  Returns 1 and
+ * fills *kind / *reason_id for those four, 0 (and kind = NXS_KIND_OTHER, reason NXS_REASON_UNKNOWN)
+ * for anything else.  Exit codes, restart counts and phases have no semantics in the reference and
+ * are not inputs anywhere in this library. */
+int nxs_ext_container_reason_to_event(const char *container_reason, size_t len, uint8_t *kind, uint16_t *reason_id);
+
 /* ------------------------------------------- checkpoint-row encoder (host) */
 /* The step right after the classification: for every job row that calls for an upsert, the three
  * columns of nexus.checkpoints (test-resources/checkpoints.cql:1-23) that superviseAction sets

@@ -60,6 +60,7 @@ SIGNATURES = {
     "nxs_free_host": (None, [C.c_void_p]),
     "nxs_intern_kind": (C.c_uint8, [C.c_char_p, C.c_size_t]),
     "nxs_intern_reason": (C.c_uint16, [C.c_char_p, C.c_size_t]),
+    "nxs_ext_container_reason_to_event": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_uint8), C.POINTER(C.c_uint16)]),
     "nxs_reason_name": (C.c_char_p, [C.c_uint32]),
     "nxs_action_name": (C.c_char_p, [C.c_uint32]),
     "nxs_stage_name": (C.c_char_p, [C.c_uint32]),

@@ -93,6 +93,15 @@ def intern_reason(s):
     return _abi.load().nxs_intern_reason(b, len(b))
 
 
+def container_reason_to_event(s):
+    """EXTENSION (no reference parity): (kind, reason_id) of the event through which a container-status reason
+    reaches the supervisor, or None for reasons that have no such event."""
+    b = s.encode()
+    kind, reason = C.c_uint8(0), C.c_uint16(0)
+    ok = _abi.load().nxs_ext_container_reason_to_event(b, len(b), C.byref(kind), C.byref(reason))
+    return (kind.value, reason.value) if ok else None
+
+
 def msg_template(i):
     return _abi.load().nxs_msg_template(i).decode()
 

@@ -106,6 +106,20 @@ uint16_t nxs_intern_reason(const char *s, size_t len) {
 }
 
 const char *nxs_reason_name(uint32_t id) { return id < 16 ? kReasonNames[id] : ""; }
+
+// EXTENSION (see the header): container-status vocabulary -> the event that carries it to the reference.
+int nxs_ext_container_reason_to_event(const char *s, size_t len, uint8_t *kind, uint16_t *reason_id) {
+  uint8_t k = NXS_KIND_OTHER;
+  uint16_t r = NXS_REASON_UNKNOWN;
+  if (s) {
+    if (eq(s, len, "OOMKilled")) k = NXS_KIND_JOB, r = NXS_REASON_POD_FAILURE_POLICY; // :311-312
+    else if (eq(s, len, "ImagePullBackOff") || eq(s, len, "CrashLoopBackOff")) k = NXS_KIND_POD, r = NXS_REASON_BACKOFF;
+    else if (eq(s, len, "ErrImagePull")) k = NXS_KIND_POD, r = NXS_REASON_FAILED;
+  }
+  if (kind) *kind = k;
+  if (reason_id) *reason_id = r;
+  return r != NXS_REASON_UNKNOWN;
+}
 const char *nxs_action_name(uint32_t a) { return a < 5 ? kActionNames[a] : ""; }
 const char *nxs_stage_name(uint32_t s) { return s < 8 ? kStageNames[s] : ""; }
 const char *nxs_msg_template(uint32_t i) { return i < 7 ? kMsgTemplates[i] : ""; }

@@ -49,6 +49,7 @@ def test_vocabulary_matches_reference_strings():
             assert nx.intern_reason(r) == i and nx.REASON[r] == i
     assert nx.intern_reason("NoSuchReason") == 0 and nx.intern_reason("") == 0
     assert [nx.intern_kind(k) for k in ("Job", "Pod", "Node", "")] == [1, 2, 0, 0]
+
     for i, s in enumerate(names["stage"]):
         assert nx.stage_name(i) == s and nx.STAGE[s] == i
     assert [nx.action_name(i) for i in range(5)] == ["", "ToFailStuckInPending", "ToFailFatalError",
@@ -63,6 +64,24 @@ def test_vocabulary_matches_reference_strings():
         tpl = nx.cause_template(v["cause_tpl"])
         assert (tpl % o["message"] if tpl else "") == o["cause"]
     assert nx.FINISHED_MASK_DEFAULT == cpu_oracle.FINISHED_MASK_DEFAULT
+
+
+def test_extension_container_reason_premap():
+    """EXTENSION, no reference parity: the north-star's container-status vocabulary mapped to the events that
+    carry it to the supervisor; classified, those events give what the reference gives for them (the oracle's
+    verdict for the OOMKilled case is the reference test's own scenario: Job PodFailurePolicy -> FAILED)."""
+    want = {"OOMKilled": ("Job", "PodFailurePolicy"), "ImagePullBackOff": ("Pod", "BackOff"),
+            "CrashLoopBackOff": ("Pod", "BackOff"), "ErrImagePull": ("Pod", "Failed")}
+    for name, (kind, reason) in want.items():
+        assert nx.container_reason_to_event(name) == (nx.intern_kind(kind), nx.intern_reason(reason)), name
+    for name in ("Completed", "ContainerCreating", "", "oomkilled"):
+        assert nx.container_reason_to_event(name) is None
+    k, r = nx.container_reason_to_event("OOMKilled")
+    cols = util.make_cols([k], [r], [7], [2], [1])  # a RUNNING run
+    _, rows = cpu_oracle.classify(cols)
+    v = nx.unpack_verdict(int(rows["verdict"][0]))
+    assert v["new_stage"] == nx.STAGE["FAILED"] and v["delete_job"] and v["upsert"]
+
 
 
 def test_shard_of_is_splitmix_mod():
