@@ -415,12 +415,16 @@ struct CopySeg {
   const void *src;
   size_t bytes;
 };
-// memcpy of a few segments, the bytes split evenly over up to 8 host threads.
+#ifndef NXS_BOUNCE_THREADS
+#define NXS_BOUNCE_THREADS 8
+#endif
+static const unsigned kBounceThreads = NXS_BOUNCE_THREADS;
+// memcpy of a few segments, the bytes split evenly over up to kBounceThreads host threads.
 static void par_copy(const CopySeg *seg, int n_seg) {
   size_t total = 0;
   for (int i = 0; i < n_seg; ++i) total += seg[i].bytes;
   const unsigned hw = std::thread::hardware_concurrency();
-  const unsigned T = (unsigned)std::min<size_t>(std::min(8u, hw ? hw : 4u), total / (4u << 20) + 1);
+  const unsigned T = (unsigned)std::min<size_t>(std::min(kBounceThreads, hw ? hw : 4u), total / (4u << 20) + 1);
   auto work = [&](unsigned t) {
     size_t lo = total * t / T, hi = total * (t + 1) / T, off = 0;
     for (int i = 0; i < n_seg && off < hi; ++i) {
@@ -453,7 +457,7 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
     }
   }
   const bool verbose = (bounce_in || bounce_out) && getenv("NXS_VERBOSE") != nullptr;
-  double t_in = 0, t_out = 0, t_wait_count = 0, t_wait_d2h = 0;
+  double t_in = 0, t_wait_count = 0, t_wait_d2h = 0;
   auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
   uint64_t lo = 0, rows_done = 0;
   uint64_t pend_lo[2] = {0, 0}, pend_n[2] = {0, 0}; // slices whose rows are still to be downloaded
@@ -481,19 +485,50 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
     pending[b] = false;
     return NXS_OK;
   };
-  auto copy_out = [&](int b) -> int { // bounce buffers of set b -> the caller's buffers, once its downloads are done
+  // Bounce buffers of set b -> the caller's buffers, once the set's downloads are done: a helper thread per
+  // slice, started when the slice's row download has been queued, so that these copies run beside the
+  // main thread's copies INTO the bounce buffers and its waits (joined before the set is used again).
+  std::thread out_thread[2];
+  int out_rc[2] = {NXS_OK, NXS_OK};
+  double out_secs[2] = {0, 0};
+  struct JoinAll { // (no exit from this function may leave a helper thread running)
+    std::thread *t;
+    ~JoinAll() {
+      for (int b = 0; b < 2; ++b)
+        if (t[b].joinable()) t[b].join();
+    }
+  } join_all{out_thread};
+  auto start_copy_out = [&](int b) {
+    if (!out_wait[b]) return;
+    uint32_t *dst_v = out->verdict ? out->verdict + out_lo[b] : nullptr;
+    nxs_job_row *dst_r = out->job_rows + out_row0[b];
+    const uint64_t n_v = out_n[b], n_r = out_jobs[b];
+    out_thread[b] = std::thread([ctx, b, dst_v, dst_r, n_v, n_r, &out_rc, &out_secs, now] {
+      if (cudaSetDevice(ctx->device) != cudaSuccess || cudaEventSynchronize(ctx->e_d2h[b]) != cudaSuccess) {
+        out_rc[b] = NXS_ERR_CUDA;
+        return;
+      }
+      const double t1 = now();
+      CopySeg seg[2];
+      int ns = 0;
+      if (dst_v) seg[ns++] = CopySeg{dst_v, ctx->h_verdict[b], n_v * 4};
+      seg[ns++] = CopySeg{dst_r, ctx->h_rows[b], n_r * sizeof(nxs_job_row)};
+      par_copy(seg, ns);
+      out_secs[b] += now() - t1;
+    });
+  };
+  auto copy_out = [&](int b) -> int { // wait for the helper of set b
     if (!out_wait[b]) return NXS_OK;
     const double t0 = now();
-    NXS_CUDA(ctx, cudaEventSynchronize(ctx->e_d2h[b]));
-    const double t1 = now();
-    t_wait_d2h += t1 - t0;
-    CopySeg seg[2];
-    int ns = 0;
-    if (out->verdict) seg[ns++] = CopySeg{out->verdict + out_lo[b], ctx->h_verdict[b], out_n[b] * 4};
-    seg[ns++] = CopySeg{out->job_rows + out_row0[b], ctx->h_rows[b], out_jobs[b] * sizeof(nxs_job_row)};
-    par_copy(seg, ns);
-    t_out += now() - t1;
+    if (out_thread[b].joinable()) out_thread[b].join();
+    t_wait_d2h += now() - t0;
     out_wait[b] = false;
+    if (out_rc[b] != NXS_OK) {
+      snprintf(ctx->err, sizeof ctx->err, "copying a slice's results to the caller's buffers failed");
+      const int r = out_rc[b];
+      out_rc[b] = NXS_OK;
+      return r;
+    }
     return NXS_OK;
   };
 
@@ -510,10 +545,7 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
     if (pending[b]) { // buffer set b still holds the slice before last: get its rows out first
       rc = finish_slice(b);
       if (rc != NXS_OK) return rc;
-    }
-    if (bounce_out) { // ... and, bounced, on to the caller before the set is written again
-      rc = copy_out(b);
-      if (rc != NXS_OK) return rc;
+      start_copy_out(b);
     }
     uint8_t *base = ctx->d_in[b];
     uint64_t *d_key = reinterpret_cast<uint64_t *>(base);
@@ -564,6 +596,11 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
     if (pending[b ^ 1]) {
       rc = finish_slice(b ^ 1);
       if (rc != NXS_OK) return rc;
+      start_copy_out(b ^ 1);
+    }
+    if (bounce_out) { // the set's previous results must have left its bounce buffers before new ones are queued into them
+      rc = copy_out(b);
+      if (rc != NXS_OK) return rc;
     }
     NXS_CUDA(ctx, cudaStreamWaitEvent(ctx->s_d2h, ctx->e_kernel[b], 0));
     NXS_CUDA(ctx, cudaMemcpyAsync(ctx->h_njobs + b, ctx->d_njobs + b, 8, cudaMemcpyDeviceToHost, ctx->s_d2h));
@@ -583,6 +620,7 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
     if (pending[o]) {
       rc = finish_slice(o);
       if (rc != NXS_OK) return rc;
+      start_copy_out(o);
     }
   }
   for (int b = 0; b < 2; ++b) {
@@ -592,8 +630,8 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
   NXS_CUDA(ctx, cudaStreamSynchronize(ctx->s_d2h));
   NXS_CUDA(ctx, cudaStreamSynchronize(s_comp));
   if (verbose)
-    fprintf(stderr, "nxs bounce: copy in %.1f ms, copy out %.1f ms, waiting for job counts %.1f ms, for downloads %.1f ms\n",
-            t_in * 1e3, t_out * 1e3, t_wait_count * 1e3, t_wait_d2h * 1e3);
+    fprintf(stderr, "nxs bounce: copy in %.1f ms, copy out (helper threads) %.1f ms, waiting for job counts %.1f ms, for the helpers %.1f ms\n",
+            t_in * 1e3, (out_secs[0] + out_secs[1]) * 1e3, t_wait_count * 1e3, t_wait_d2h * 1e3);
   *out->n_jobs = rows_done;
   return NXS_OK;
 }

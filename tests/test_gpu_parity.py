@@ -219,6 +219,12 @@ def test_host_path_error_after_enqueued_slices_leaves_nothing_in_flight():
             lib.nxs_free_host(p)
         small = util.random_cols(rng, 3_000_000, 40)
         util.assert_same(*c.classify(small), *cpu_oracle.classify(small, threads=4), "after the failed call")
+        # the same failure with ordinary pageable buffers (bounce buffers and their helper threads in play)
+        launched = c.launches
+        with pytest.raises(nx.NxsError) as e:
+            c.classify(cols)
+        assert e.value.status == nx._abi.NXS_ERR_CAPACITY and c.launches > launched
+        util.assert_same(*c.classify(small), *cpu_oracle.classify(small, threads=4), "after the failed pageable call")
         # the whole batch still goes through the device-resident entry point, as the error text says
         import torch
         dev = {k: torch.from_numpy(v.view(np.uint8).copy()).cuda() for k, v in cols.items()}
