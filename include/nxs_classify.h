@@ -187,7 +187,7 @@ typedef struct nxs_batch_packed {
 
 typedef struct nxs_out {
   uint32_t *verdict;     /* n; may be NULL: per-record verdicts are then not produced
-                            (nxs_classify, nxs_classify_packed, nxs_classify_device)  */
+                            (every entry point that takes an nxs_out)                 */
   nxs_job_row *job_rows; /* capacity >= number of jobs (n is always enough) */
   uint64_t *n_jobs;      /* 1 element                                       */
 } nxs_out;

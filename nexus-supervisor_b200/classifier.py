@@ -277,8 +277,9 @@ class ShardedClassifier:
     def __exit__(self, *exc):
         self.close()
 
-    def classify(self, cols, out_verdict=None, out_rows=None):
-        """Same contract as Classifier.classify: (verdict u32[n], rows JOB_ROW[n_jobs]) in stream order."""
+    def classify(self, cols, out_verdict=None, out_rows=None, want_verdict=True):
+        """Same contract as Classifier.classify: (verdict u32[n], rows JOB_ROW[n_jobs]) in stream order; verdict is
+        None with want_verdict=False (job rows only: nothing per record is produced, downloaded or merged)."""
         kind = np.ascontiguousarray(cols["kind"], dtype=np.uint8)
         reason = np.ascontiguousarray(cols["reason_id"], dtype=np.uint16)
         flags = np.ascontiguousarray(cols["flags"], dtype=np.uint8)
@@ -287,13 +288,15 @@ class ShardedClassifier:
         n = len(kind)
         if not (len(reason) == len(flags) == len(stage) == len(key) == n):
             raise ValueError("columns differ in length")
-        verdict = out_verdict if out_verdict is not None else np.empty(n, dtype=np.uint32)
+        verdict = None
+        if want_verdict:
+            verdict = out_verdict if out_verdict is not None else np.empty(n, dtype=np.uint32)
         rows = out_rows if out_rows is not None else np.empty(n, dtype=JOB_ROW)
         n_jobs = C.c_uint64(0)
         batch = _abi.Batch(kind.ctypes.data, reason.ctypes.data, flags.ctypes.data, stage.ctypes.data,
                            key.ctypes.data, n)
-        out = _abi.Out(verdict.ctypes.data, rows.ctypes.data, C.addressof(n_jobs))
+        out = _abi.Out(verdict.ctypes.data if want_verdict else None, rows.ctypes.data, C.addressof(n_jobs))
         rc = self._lib.nxs_classify_sharded(self._h, C.byref(batch), C.byref(out))
         if rc != _abi.NXS_OK:
             raise NxsError(rc, self._lib.nxs_sharded_last_error(self._h).decode())
-        return verdict[:n], rows[:n_jobs.value]
+        return (verdict[:n] if want_verdict else None), rows[:n_jobs.value]

@@ -777,7 +777,7 @@ extern "C" int nxs_classify_device_noalloc(int device, void *cuda_stream, uint16
   }
   cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
   if (in->n == 0) return cudaMemsetAsync(out->n_jobs, 0, sizeof(uint64_t), stream) == cudaSuccess ? NXS_OK : NXS_ERR_CUDA;
-  if (!in->kind || !in->reason_id || !in->flags || !in->cur_stage || !in->job_key || !out->verdict || !out->job_rows)
+  if (!in->kind || !in->reason_id || !in->flags || !in->cur_stage || !in->job_key || !out->job_rows)
     return NXS_ERR_ARG;
   if (!aligned16(in->kind) || !aligned16(in->reason_id) || !aligned16(in->flags) || !aligned16(in->cur_stage) ||
       !aligned16(in->job_key) || !aligned16(out->job_rows) || (reinterpret_cast<uintptr_t>(out->verdict) & 3u))

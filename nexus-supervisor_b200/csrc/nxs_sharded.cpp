@@ -15,6 +15,7 @@
 #include <cstring>
 #include <new>
 #include <thread>
+#include <type_traits>
 #include <vector>
 
 #include "nxs_host.h"
@@ -197,7 +198,7 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
     *out->n_jobs = 0;
     return NXS_OK;
   }
-  if (!in->kind || !in->reason_id || !in->flags || !in->cur_stage || !in->job_key || !out->verdict || !out->job_rows) {
+  if (!in->kind || !in->reason_id || !in->flags || !in->cur_stage || !in->job_key || !out->job_rows) {
     snprintf(h->err, sizeof h->err, "null column pointer");
     return NXS_ERR_ARG;
   }
@@ -314,7 +315,7 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
       if (b.n == 0) return;
       nxs_batch sin{b.kind, b.reason, b.flags, b.stage, b.key, b.n};
       uint64_t jobs = 0;
-      nxs_out sout{b.verdict, b.rows, &jobs};
+      nxs_out sout{out->verdict ? b.verdict : nullptr, b.rows, &jobs}; // (rows only when the caller wants no per-record verdicts)
       b.rc = classify(user, s, &sin, &sout);
       if (b.rc != NXS_OK) return;
       if (jobs != b.n_jobs) b.rc = NXS_ERR_CUDA;
@@ -336,7 +337,8 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
   // shard's cursors; a winner index is shard-local and moves with the job's first record.  The row is
   // written for every record of a job and the output cursor advances only behind the last one (a chunk
   // ends on a job boundary, so every such early write is overwritten from inside the chunk).
-  parallel([&](unsigned t) {
+  auto gather = [&](unsigned t, auto want_verdict) {
+    constexpr bool kVerdict = decltype(want_verdict)::value;
     uint64_t rpos[256], r[256]; // this chunk's cursors in every shard's buffers: records and job rows
     const uint32_t *sv[256];
     const nxs_job_row *sr[256];
@@ -354,7 +356,7 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
     auto one = [&](uint64_t i, uint64_t k, bool tail) {
       const uint32_t s = shard_of(k);
       const uint64_t p = rpos[s]++;
-      v[i] = sv[s][p];
+      if constexpr (kVerdict) v[i] = sv[s][p];
       const bool head = k != prev;
       first_i = head ? i : first_i; // where the job begins: in the stream, and in its shard
       p0 = head ? p : p0;
@@ -368,7 +370,9 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
     };
     for (uint64_t i = lo; i + 1 < hi; ++i) one(i, key[i], key[i + 1] != key[i]);
     one(hi - 1, key[hi - 1], true);
-  });
+  };
+  if (out->verdict) parallel([&](unsigned t) { gather(t, std::true_type{}); });
+  else parallel([&](unsigned t) { gather(t, std::false_type{}); });
   lap("gather (verdicts, job rows)");
   *out->n_jobs = total_jobs;
   return NXS_OK;

@@ -27,6 +27,8 @@ def test_sharded_equals_one_unsharded_oracle_run(G):
             want_v, want_r = cpu_oracle.classify(cols, threads=cpu_oracle.hardware_threads())
             got_v, got_r = sc.classify(cols)
             util.assert_same(got_v, got_r, want_v, want_r, f"G={G} max_len={max_len}")
+            none_v, rows_only = sc.classify(cols, want_verdict=False)
+            assert none_v is None and np.array_equal(rows_only, want_r)
 
 
 def test_sharded_synthetic_stream_and_small_batches():

@@ -127,7 +127,8 @@ def test_product_partition_and_gather_with_the_oracle_as_classifier(G):
                 "cur_stage": arr(b.cur_stage, np.uint8), "job_key": arr(b.job_key, np.uint64)}
         assert all(nx.shard_of(int(k), G) == shard for k in cols["job_key"][:20])
         v, r = cpu_oracle.classify(cols)
-        arr(o.verdict, np.uint32)[:] = v
+        if o.verdict:
+            arr(o.verdict, np.uint32)[:] = v
         np.frombuffer((C.c_uint8 * (16 * len(r))).from_address(o.job_rows), dtype=cpu_oracle.JOB_ROW)[:] = r
         C.c_uint64.from_address(o.n_jobs).value = len(r)
         seen[shard] = n
@@ -151,3 +152,8 @@ def test_product_partition_and_gather_with_the_oracle_as_classifier(G):
         assert lib.nxs_internal_sharded_run(G, C.byref(batch), C.byref(out), FN(classify_shard), None) == 0
         assert sum(seen.values()) == n
         util.assert_same(verdict, rows[:nj.value], *cpu_oracle.classify(cols), f"G={G} n={n}")
+        # job rows only (out->verdict == NULL): nothing per record is asked of the shards or merged
+        rows2 = np.zeros(n, cpu_oracle.JOB_ROW)
+        out2 = nx._abi.Out(None, rows2.ctypes.data, C.addressof(nj))
+        assert lib.nxs_internal_sharded_run(G, C.byref(batch), C.byref(out2), FN(classify_shard), None) == 0
+        assert np.array_equal(rows2[:nj.value], rows[:nj.value])

@@ -71,6 +71,13 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row():
             ora_v, ora_r = cpu_oracle.classify(cols, fm, threads=4)
             host_r = got_r[:jobs].cpu().numpy().view(np.uint64).reshape(-1, 2).copy().view(cpu_oracle.JOB_ROW).reshape(-1)
             util.assert_same(got_v.cpu().numpy().view(np.uint32), host_r, ora_v, ora_r, f"no-alloc call {call} vs oracle")
+            # job rows only (out->verdict == NULL), as on the other entry points
+            rows_only, n_only = torch.zeros((n, 2), dtype=torch.int64, device="cuda"), torch.zeros(1, dtype=torch.int64, device="cuda")
+            batch = nx._abi.Batch(ptr["kind"], ptr["reason_id"], ptr["flags"], ptr["cur_stage"], ptr["job_key"], n)
+            out = nx._abi.Out(None, rows_only.data_ptr(), n_only.data_ptr())
+            assert lib.nxs_classify_device_noalloc(0, C.c_void_p(stream), fm, C.byref(batch), C.byref(out)) == nx._abi.NXS_OK
+            torch.cuda.synchronize()
+            assert int(n_only.item()) == jobs and torch.equal(rows_only[:jobs], want_r[:jobs])
             del keep
 
 
