@@ -54,29 +54,39 @@ def pack_columns(cols, out=None):
     return attr
 
 
-def encode_checkpoint_rows(rows, msg_heap=None, msg_offsets=None):
+def encode_checkpoint_rows(rows, msg_heap=None, msg_offsets=None, out=None):
     """nxs_encode_checkpoint_rows: (arena u8[], offsets u64[3u+1], update_row u32[u], update_flags u8[u]) for the
-    job rows that upsert.  msg_heap / msg_offsets: the events' Message bytes per batch record."""
+    job rows that upsert.  msg_heap / msg_offsets: the events' Message bytes per batch record.  `out`: four
+    arrays to write into — arena u8[enough bytes, else NXS_ERR_CAPACITY], offsets u64[3 * len(rows) + 1],
+    update_row u32[len(rows)], update_flags u8[len(rows)] (a caller that encodes batch after batch keeps its buffers) — without it the sizes are queried first and fresh arrays made."""
     lib = _abi.load()
     rows = np.ascontiguousarray(rows, dtype=JOB_ROW)
     n_rec = 0 if msg_offsets is None else len(msg_offsets) - 1
     heap_p = None if msg_heap is None else np.ascontiguousarray(msg_heap, dtype=np.uint8).ctypes.data
     offs_p = None if msg_offsets is None else np.ascontiguousarray(msg_offsets, dtype=np.uint64).ctypes.data
     n_up, n_bytes = C.c_uint64(0), C.c_uint64(0)
-    rc = lib.nxs_encode_checkpoint_rows(rows.ctypes.data, len(rows), heap_p, offs_p, n_rec, None, None, 0, None, None,
-                                        None, C.byref(n_up), C.byref(n_bytes))
-    if rc != _abi.NXS_OK:
-        raise NxsError(rc, "nxs_encode_checkpoint_rows (size query)")
-    arena = np.empty(n_bytes.value, dtype=np.uint8)
-    offsets = np.empty(3 * n_up.value + 1, dtype=np.uint64)
-    update_row = np.empty(n_up.value, dtype=np.uint32)
-    update_flags = np.empty(n_up.value, dtype=np.uint8)
+    if out is None:
+        rc = lib.nxs_encode_checkpoint_rows(rows.ctypes.data, len(rows), heap_p, offs_p, n_rec, None, None, 0, None, None,
+                                            None, C.byref(n_up), C.byref(n_bytes))
+        if rc != _abi.NXS_OK:
+            raise NxsError(rc, "nxs_encode_checkpoint_rows (size query)")
+        arena = np.empty(n_bytes.value, dtype=np.uint8)
+        offsets = np.empty(3 * n_up.value + 1, dtype=np.uint64)
+        update_row = np.empty(n_up.value, dtype=np.uint32)
+        update_flags = np.empty(n_up.value, dtype=np.uint8)
+    else:
+        arena, offsets, update_row, update_flags = out
+        if len(offsets) < 3 * len(update_row) + 1 or len(update_flags) < len(update_row) or len(update_row) < len(rows):
+            # (the C call checks the arena against the bytes it needs; the per-update arrays have no capacity
+            # argument, so they must hold the worst case: one update per job row)
+            raise ValueError("out: update_row / update_flags need len(rows) entries, offsets 3 * len(rows) + 1")
     rc = lib.nxs_encode_checkpoint_rows(rows.ctypes.data, len(rows), heap_p, offs_p, n_rec, None, arena.ctypes.data,
                                         arena.nbytes, offsets.ctypes.data, update_row.ctypes.data,
                                         update_flags.ctypes.data, C.byref(n_up), C.byref(n_bytes))
     if rc != _abi.NXS_OK:
         raise NxsError(rc, "nxs_encode_checkpoint_rows")
-    return arena, offsets, update_row, update_flags
+    u = n_up.value
+    return arena[:n_bytes.value], offsets[:3 * u + 1], update_row[:u], update_flags[:u]
 
 
 def shard_of(job_key, n_shards):

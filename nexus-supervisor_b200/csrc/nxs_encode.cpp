@@ -20,21 +20,35 @@
 
 namespace {
 
+// A fixed string of the vocabulary with zero bytes behind it up to a multiple of 32 (and one block more): the
+// encoder copies it in whole 32-byte blocks.
+struct Tpl {
+  std::string buf;
+  size_t len = 0;
+  void set(const std::string &x) {
+    len = x.size();
+    buf = x;
+    buf.resize(((len + 31) & ~size_t(31)) + 32, '\0');
+  }
+  size_t size() const { return len; }
+  const char *data() const { return buf.data(); }
+};
 struct Tables {
-  std::string stage[16];
-  std::string cause[4][8];
+  Tpl stage[16];
+  Tpl cause[4][8];
 };
 
 Tables build_tables(const char *const *stage_names) {
   Tables t;
-  for (uint32_t s = 0; s < 16; ++s) t.stage[s] = stage_names ? (stage_names[s] ? stage_names[s] : "") : nxs_stage_name(s);
+  for (uint32_t s = 0; s < 16; ++s) t.stage[s].set(stage_names ? (stage_names[s] ? stage_names[s] : "") : nxs_stage_name(s));
   for (uint32_t c = 1; c < 4; ++c)
     for (uint32_t m = 0; m < 8; ++m) {
       const char *fmt = nxs_cause_template(c), *msg = nxs_msg_template(m);
       std::string out(strlen(fmt) + strlen(msg) + 1, '\0');
       out.resize((size_t)snprintf(out.data(), out.size(), fmt, msg)); // :298, :325, :350
-      t.cause[c][m] = out;
+      t.cause[c][m].set(out);
     }
+  for (Tpl &x : t.cause[0]) x.set("");
   return t;
 }
 
@@ -86,23 +100,47 @@ extern "C" int nxs_encode_checkpoint_rows(const nxs_job_row *rows, uint64_t n_ro
     uint64_t lo, hi;
     range(k, lo, hi);
     uint64_t u = cnt[k], pos = bytes[k];
-    auto put = [&](const void *src, uint64_t len) {
+    const uint64_t region_end = bytes[k + 1];
+    const uint64_t heap_bytes = msg_offsets ? msg_offsets[n_records] : 0;
+    auto put = [&](const void *src, uint64_t len) { // bytes of unknown origin: exact copy
       memcpy(arena + pos, src, len);
+      pos += len;
+    };
+    // A template string (Tpl: zero-padded to whole 32-byte blocks) is copied
+    // in 32-byte blocks — constant-size moves instead of a library call per field — as long as the blocks
+    // stay inside this thread's part of the arena; what a block writes behind the field is overwritten by
+    // the next field.
+    auto put_tpl = [&](const Tpl &str) {
+      const uint64_t len = str.size(), padded = (len + 31) & ~uint64_t(31);
+      if (pos + padded <= region_end) {
+        const char *src = str.data();
+        for (uint64_t o = 0; o < padded; o += 32) memcpy(arena + pos + o, src + o, 32);
+      } else {
+        memcpy(arena + pos, str.data(), len);
+      }
       pos += len;
     };
     for (uint64_t r = lo; r < hi; ++r) {
       const uint32_t v = rows[r].verdict;
       if (!NXS_V_UPSERT(v)) continue;
       const uint32_t c = NXS_V_CAUSE_TPL(v);
-      const std::string &stage = t.stage[NXS_V_NEW_STAGE(v)];
+      const Tpl &stage = t.stage[NXS_V_NEW_STAGE(v)];
       offsets[3 * u] = pos;
-      put(stage.data(), stage.size()); // :297, :324, :349, :362
+      put_tpl(stage); // :297, :324, :349, :362
       offsets[3 * u + 1] = pos;
-      if (c) put(t.cause[c][NXS_V_MSG_TPL(v)].data(), t.cause[c][NXS_V_MSG_TPL(v)].size());
+      if (c) put_tpl(t.cause[c][NXS_V_MSG_TPL(v)]);
       offsets[3 * u + 2] = pos;
       if (c) { // :299, :326, :351
         const uint64_t len = details_len(rows[r], msg_offsets, n_records);
-        if (len) put(msg_heap + msg_offsets[rows[r].winner_idx], len);
+        if (len) {
+          const uint64_t at = msg_offsets[rows[r].winner_idx];
+          if (len <= 32 && pos + 32 <= region_end && at + 32 <= heap_bytes) { // a short message: one fixed-size block
+            memcpy(arena + pos, msg_heap + at, 32);
+            pos += len;
+          } else {
+            put(msg_heap + at, len);
+          }
+        }
       }
       update_row[u] = (uint32_t)r;
       if (update_flags) update_flags[u] = (uint8_t)((c ? 1u : 0u) | (NXS_V_DELETE_JOB(v) ? 2u : 0u));

@@ -77,3 +77,28 @@ def test_encoder_size_query_and_capacity():
     rc = lib.nxs_encode_checkpoint_rows(rows.ctypes.data, len(rows), None, None, 0, None, small.ctypes.data, 8,
                                         offs.ctypes.data, upd.ctypes.data, None, C.byref(n_up), C.byref(n_bytes))
     assert rc == nx._abi.NXS_ERR_CAPACITY
+
+
+def test_encoder_into_kept_buffers():
+    """out=: a caller that encodes batch after batch writes into buffers it keeps; same bytes as a fresh call,
+    stale content of an earlier, larger batch does not leak, a short arena is refused."""
+    big = cpu_oracle.generate(nx.WORKLOAD_SKEWED, 200_000)
+    small = cpu_oracle.generate(nx.WORKLOAD_SKEWED, 30_000, first=1_000_000)
+    bufs = None
+    for cols in (big, small):
+        _, rows = cpu_oracle.classify(cols)
+        n = len(cols["kind"])
+        heap = np.frombuffer(b"".join(b"m%d" % i for i in range(n)), np.uint8)
+        lens = np.array([len(b"m%d" % i) for i in range(n)], np.uint64)
+        offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+        want = nx.encode_checkpoint_rows(rows, heap, offs)
+        if bufs is None:
+            m = len(rows)
+            bufs = (np.full(want[0].nbytes + 100, 0xEE, np.uint8), np.full(3 * m + 1, 7, np.uint64),
+                    np.full(m, 9, np.uint32), np.full(m, 3, np.uint8))
+        got = nx.encode_checkpoint_rows(rows, heap, offs, out=bufs)
+        assert all(np.array_equal(a, b) for a, b in zip(got, want))
+    with pytest.raises(nx.NxsError) as e:
+        _, rows = cpu_oracle.classify(big)
+        nx.encode_checkpoint_rows(rows, out=(np.empty(16, np.uint8),) + bufs[1:])
+    assert e.value.status == nx._abi.NXS_ERR_CAPACITY
