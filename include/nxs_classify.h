@@ -219,6 +219,10 @@ int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out);
  * out->verdict == NULL only the job rows come down — the layout for callers behind PCIe, who act
  * on job rows anyway.  The attr column is expanded into the four byte columns on the device. */
 int nxs_classify_packed(nxs_ctx *ctx, const nxs_batch_packed *in, const nxs_out *out);
+/* Bytes the last nxs_classify / nxs_classify_packed call of this ctx moved over the host link, as queued
+ * (measurement aid: batches of more than one slice upload the four small columns packed into 16 bits —
+ * 10 instead of 13 bytes per record — because the kernel reads no more of them). */
+void nxs_last_wire_bytes(const nxs_ctx *ctx, uint64_t *h2d_bytes, uint64_t *d2h_bytes);
 /* Host helper of the flattening layer: attr[i] = NXS_ATTR_PACK(kind[i], reason_id[i], flags[i], cur_stage[i]). */
 void nxs_pack_columns(const uint8_t *kind, const uint16_t *reason_id, const uint8_t *flags,
                       const uint8_t *cur_stage, uint64_t n, uint16_t *attr);

@@ -55,6 +55,7 @@ SIGNATURES = {
     "nxs_classify_device": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(Out)]),
     "nxs_launch_count": (C.c_uint64, [C.c_void_p]),
     "nxs_last_tile": (C.c_int, [C.c_void_p]),
+    "nxs_last_wire_bytes": (None, [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "nxs_classify_device_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_uint16, C.POINTER(Batch), C.POINTER(Out)]),
     "nxs_alloc_host": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
     "nxs_free_host": (None, [C.c_void_p]),

@@ -182,6 +182,13 @@ class Classifier:
         """Records per tile of the kernel variant the last launch used."""
         return int(self._lib.nxs_last_tile(self._ctx))
 
+    @property
+    def last_wire_bytes(self):
+        """(host->device, device->host) bytes the last host-pointer call moved over the link."""
+        up, down = C.c_uint64(0), C.c_uint64(0)
+        self._lib.nxs_last_wire_bytes(self._ctx, C.byref(up), C.byref(down))
+        return int(up.value), int(down.value)
+
     # ------------------------------------------------------------- host path
     def classify(self, cols, out_verdict=None, out_rows=None, want_verdict=True):
         """cols: dict of numpy arrays kind u8, reason_id u16, flags u8, cur_stage u8, job_key u64.

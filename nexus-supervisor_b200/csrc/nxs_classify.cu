@@ -39,6 +39,11 @@ struct nxs_ctx {
   uint8_t *d_in[2] = {nullptr, nullptr};
   uint32_t *d_verdict[2] = {nullptr, nullptr};
   nxs_job_row *d_rows[2] = {nullptr, nullptr};
+  uint64_t wire_h2d = 0, wire_d2h = 0; // bytes the last host-pointer call moved over the link
+  cudaEvent_t e_codes[2] = {nullptr, nullptr}; // a slice's verdict bytes have arrived in h_codes
+  uint8_t *h_codes[2] = {nullptr, nullptr}; // page-locked: a slice's per-record verdicts as bytes, before their expansion
+  uint32_t verdict_of[256];                 // verdict_of_code() of every byte
+  uint16_t *h_attr[2] = {nullptr, nullptr}; // page-locked: the four small columns of a slice, packed for the upload
   uint64_t *d_njobs = nullptr; // 2 counters
   uint64_t *h_njobs = nullptr; // pinned, 2 counters
   // page-locked bounce buffers for callers whose own buffers are pageable (allocated on first such call)
@@ -175,6 +180,7 @@ int nxs_create(int device, uint64_t max_records, uint16_t finished_mask, nxs_ctx
   for (uint32_t a = 1; a <= 4; ++a)
     if ((finished_mask >> new_stage_of(a)) & 1u) ctx->term_mask |= 1u << a;
   nxs_build_lut(ctx->lut, ctx->code);
+  for (uint32_t b = 0; b < 256; ++b) ctx->verdict_of[b] = verdict_of_code(b, ctx->code, ctx->term_mask);
   int rc = NXS_OK;
   auto bail = [&](int code) {
     nxs_destroy(ctx);
@@ -225,7 +231,10 @@ void nxs_destroy(nxs_ctx *ctx) {
     cudaFree(ctx->d_in[b]);
     cudaFree(ctx->d_verdict[b]);
     cudaFree(ctx->d_rows[b]);
+    if (ctx->h_attr[b]) cudaFreeHost(ctx->h_attr[b]);
+    if (ctx->h_codes[b]) cudaFreeHost(ctx->h_codes[b]);
     if (ctx->e_h2d[b]) cudaEventDestroy(ctx->e_h2d[b]);
+    if (ctx->e_codes[b]) cudaEventDestroy(ctx->e_codes[b]);
     if (ctx->e_kernel[b]) cudaEventDestroy(ctx->e_kernel[b]);
     if (ctx->e_count[b]) cudaEventDestroy(ctx->e_count[b]);
     if (ctx->e_d2h[b]) cudaEventDestroy(ctx->e_d2h[b]);
@@ -265,7 +274,8 @@ int nxs_sync(nxs_ctx *ctx) {
 uint64_t nxs_launch_count(const nxs_ctx *ctx) { return ctx ? ctx->launches : 0; }
 int nxs_last_tile(const nxs_ctx *ctx) { return ctx ? ctx->last_tile : 0; }
 
-static int launch_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out, uint32_t record_base);
+static int launch_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out, uint32_t record_base,
+                           uint8_t *verdict_code = nullptr);
 
 int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
   return launch_classify(ctx, in, out, 0);
@@ -273,7 +283,9 @@ int nxs_classify_device(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out) {
 
 // Validates device pointers and enqueues one classification launch on the ctx stream.
 // record_base is added to every winner_idx (used when a batch is processed in slices).
-static int launch_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out, uint32_t record_base) {
+// verdict_code != nullptr (host-pointer path only): one byte per record instead of out->verdict, which is then null.
+static int launch_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out, uint32_t record_base,
+                           uint8_t *verdict_code) {
   if (!ctx || !in || !out) return NXS_ERR_ARG;
   if (!out->n_jobs) return fail_arg(ctx, "out->n_jobs is null");
   if (in->n > ctx->max_records) {
@@ -304,6 +316,7 @@ static int launch_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out
   p.stage = in->cur_stage;
   p.key = in->job_key;
   p.verdict = out->verdict;
+  p.verdict_code = verdict_code;
   p.rows = out->job_rows;
   p.n_jobs = out->n_jobs;
   p.desc = ctx->desc;
@@ -349,7 +362,8 @@ static int ensure_staging(nxs_ctx *ctx, uint64_t slice) {
       if (cudaEventCreateWithFlags(&ctx->e_h2d[b], cudaEventDisableTiming) != cudaSuccess ||
           cudaEventCreateWithFlags(&ctx->e_kernel[b], cudaEventDisableTiming) != cudaSuccess ||
           cudaEventCreateWithFlags(&ctx->e_count[b], cudaEventDisableTiming) != cudaSuccess ||
-          cudaEventCreateWithFlags(&ctx->e_d2h[b], cudaEventDisableTiming) != cudaSuccess)
+          cudaEventCreateWithFlags(&ctx->e_d2h[b], cudaEventDisableTiming) != cudaSuccess ||
+          cudaEventCreateWithFlags(&ctx->e_codes[b], cudaEventDisableTiming) != cudaSuccess)
         return NXS_ERR_CUDA;
     }
   }
@@ -359,15 +373,21 @@ static int ensure_staging(nxs_ctx *ctx, uint64_t slice) {
     cudaFree(ctx->d_in[b]);
     cudaFree(ctx->d_verdict[b]);
     cudaFree(ctx->d_rows[b]);
+    if (ctx->h_attr[b]) cudaFreeHost(ctx->h_attr[b]);
+    if (ctx->h_codes[b]) cudaFreeHost(ctx->h_codes[b]);
+    ctx->h_codes[b] = nullptr;
     ctx->d_in[b] = nullptr;
     ctx->d_verdict[b] = nullptr;
     ctx->d_rows[b] = nullptr;
+    ctx->h_attr[b] = nullptr;
   }
   ctx->staged_records = 0;
   for (int b = 0; b < 2; ++b) {
     if (cudaMalloc(&ctx->d_in[b], cap * 13) != cudaSuccess) return NXS_ERR_NOMEM;
     if (cudaMalloc(&ctx->d_verdict[b], cap * 4) != cudaSuccess) return NXS_ERR_NOMEM;
     if (cudaMalloc(&ctx->d_rows[b], cap * sizeof(nxs_job_row)) != cudaSuccess) return NXS_ERR_NOMEM;
+    if (cudaMallocHost(&ctx->h_attr[b], cap * sizeof(uint16_t)) != cudaSuccess) return NXS_ERR_NOMEM;
+    if (cudaMallocHost(&ctx->h_codes[b], cap) != cudaSuccess) return NXS_ERR_NOMEM;
   }
   ctx->staged_records = cap;
   return NXS_OK;
@@ -439,7 +459,39 @@ static void par_copy(const CopySeg *seg, int n_seg) {
   for (std::thread &x : th) x.join();
 }
 
+// dst[i] = table[codes[i]]: the per-record verdicts of a slice from their one-byte form, over a few host threads.
+static void expand_codes(const uint8_t *codes, uint64_t n, const uint32_t *table, uint32_t *dst) {
+  const unsigned hw = std::thread::hardware_concurrency();
+  const unsigned T = (unsigned)std::min<uint64_t>(std::min(kBounceThreads, hw ? hw : 4u), n / (1u << 20) + 1);
+  auto work = [=](unsigned t) {
+    for (uint64_t i = n * t / T, e = n * (t + 1) / T; i < e; ++i) dst[i] = table[codes[i]];
+  };
+  std::vector<std::thread> th;
+  for (unsigned t = 1; t < T; ++t) th.emplace_back(work, t);
+  work(0);
+  for (std::thread &x : th) x.join();
+}
+
+// attr[i] = NXS_ATTR_PACK(...) for i in [0, n): a streaming loop (one thread moves ~1.4e9 records/s), split over a
+// few host threads for large n.
+static void pack_columns(const uint8_t *kind, const uint16_t *reason_id, const uint8_t *flags, const uint8_t *cur_stage,
+                         uint64_t n, uint16_t *attr) {
+  const unsigned hw = std::thread::hardware_concurrency();
+  const unsigned T = (unsigned)std::min<uint64_t>(std::min(16u, hw ? hw : 4u), n / (1u << 20) + 1);
+  auto work = [=](unsigned t) {
+    for (uint64_t i = n * t / T, e = n * (t + 1) / T; i < e; ++i)
+      attr[i] = (uint16_t)NXS_ATTR_PACK(kind[i], reason_id[i], flags[i], cur_stage[i]);
+  };
+  std::vector<std::thread> th;
+  for (unsigned t = 1; t < T; ++t) th.emplace_back(work, t);
+  work(0);
+  for (std::thread &x : th) x.join();
+}
+
 // `attr` != nullptr: the batch is packed (job_key + attr); the four small columns of `in` are unused.
+// Otherwise the library packs them itself, slice by slice, on their way to the GPU: the kernel reads only
+// 6 + 2 + 3 + 4 bits of them (reasons above 32 and kinds above 2 are `default` to both switches), so 10
+// instead of 13 bytes per record cross the link and nothing else changes (NXS_NO_AUTOPACK=1 turns it off).
 static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *attr, const nxs_out *out,
                            uint64_t slice_cap) {
   const uint64_t n = in->n;
@@ -456,7 +508,18 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
       return brc;
     }
   }
-  const bool verbose = (bounce_in || bounce_out) && getenv("NXS_VERBOSE") != nullptr;
+  // multi-slice batches: the small columns travel packed (the packing of slice k+1 hides behind the upload of slice k)
+  static const bool no_autopack = getenv("NXS_NO_AUTOPACK") != nullptr;
+  const bool autopack = !attr && !no_autopack && n > slice_cap;
+  const bool packed = attr != nullptr || autopack;
+  // ... and the per-record verdicts come back as one byte each (4 * arm | 32 * gate | 128 * finished: what the
+  // 32-bit verdict is a function of), expanded into the caller's array by the helper threads below
+  // (NXS_NO_VERDICT_CODES=1 turns it off)
+  static const bool no_codes = getenv("NXS_NO_VERDICT_CODES") != nullptr;
+  const bool codes = out->verdict != nullptr && !no_codes && n > slice_cap;
+  const bool helpers = bounce_out || codes; // results pass through host staging: a helper thread per slice finishes them
+  ctx->wire_h2d = 0, ctx->wire_d2h = 0;
+  const bool verbose = (bounce_in || helpers || autopack) && getenv("NXS_VERBOSE") != nullptr;
   double t_in = 0, t_wait_count = 0, t_wait_d2h = 0;
   auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
   uint64_t lo = 0, rows_done = 0;
@@ -479,6 +542,7 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
     nxs_job_row *dst = bounce_out ? ctx->h_rows[b] : out->job_rows + rows_done;
     NXS_CUDA(ctx, cudaMemcpyAsync(dst, ctx->d_rows[b], jobs * sizeof(nxs_job_row), cudaMemcpyDeviceToHost, ctx->s_d2h));
     NXS_CUDA(ctx, cudaEventRecord(ctx->e_d2h[b], ctx->s_d2h));
+    ctx->wire_d2h += jobs * sizeof(nxs_job_row) + 8;
     out_row0[b] = rows_done;
     out_jobs[b] = jobs;
     rows_done += jobs;
@@ -488,22 +552,37 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
   // Bounce buffers of set b -> the caller's buffers, once the set's downloads are done: a helper thread per
   // slice, started when the slice's row download has been queued, so that these copies run beside the
   // main thread's copies INTO the bounce buffers and its waits (joined before the set is used again).
-  std::thread out_thread[2];
-  int out_rc[2] = {NXS_OK, NXS_OK};
-  double out_secs[2] = {0, 0};
+  // The verdict bytes of a slice are expanded into the caller's array by a helper of their own, started the
+  // moment their download is queued: it needs neither the job count nor the rows.
+  std::thread out_thread[4]; // [0..1] rows (and 32-bit verdicts) out of the bounce buffers, [2..3] verdict bytes
+  std::thread *const code_thread = out_thread + 2;
+  int out_rc[2] = {NXS_OK, NXS_OK}, code_rc[2] = {NXS_OK, NXS_OK};
+  double out_secs[2] = {0, 0}, code_secs[2] = {0, 0};
   struct JoinAll { // (no exit from this function may leave a helper thread running)
     std::thread *t;
     ~JoinAll() {
-      for (int b = 0; b < 2; ++b)
+      for (int b = 0; b < 4; ++b)
         if (t[b].joinable()) t[b].join();
     }
   } join_all{out_thread};
+  auto start_expand = [&](int b, uint64_t first, uint64_t count) {
+    uint32_t *dst = out->verdict + first;
+    code_thread[b] = std::thread([ctx, b, dst, count, &code_rc, &code_secs, now] {
+      if (cudaSetDevice(ctx->device) != cudaSuccess || cudaEventSynchronize(ctx->e_codes[b]) != cudaSuccess) {
+        code_rc[b] = NXS_ERR_CUDA;
+        return;
+      }
+      const double t1 = now();
+      expand_codes(ctx->h_codes[b], count, ctx->verdict_of, dst);
+      code_secs[b] += now() - t1;
+    });
+  };
   auto start_copy_out = [&](int b) {
-    if (!out_wait[b]) return;
+    if (!out_wait[b] || !bounce_out) return;
     uint32_t *dst_v = out->verdict ? out->verdict + out_lo[b] : nullptr;
     nxs_job_row *dst_r = out->job_rows + out_row0[b];
     const uint64_t n_v = out_n[b], n_r = out_jobs[b];
-    out_thread[b] = std::thread([ctx, b, dst_v, dst_r, n_v, n_r, &out_rc, &out_secs, now] {
+    out_thread[b] = std::thread([ctx, b, dst_v, dst_r, n_v, n_r, &out_rc, &out_secs, now, codes, bounce_out] {
       if (cudaSetDevice(ctx->device) != cudaSuccess || cudaEventSynchronize(ctx->e_d2h[b]) != cudaSuccess) {
         out_rc[b] = NXS_ERR_CUDA;
         return;
@@ -511,22 +590,23 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
       const double t1 = now();
       CopySeg seg[2];
       int ns = 0;
-      if (dst_v) seg[ns++] = CopySeg{dst_v, ctx->h_verdict[b], n_v * 4};
-      seg[ns++] = CopySeg{dst_r, ctx->h_rows[b], n_r * sizeof(nxs_job_row)};
-      par_copy(seg, ns);
+      if (bounce_out && dst_v && !codes) seg[ns++] = CopySeg{dst_v, ctx->h_verdict[b], n_v * 4};
+      if (bounce_out) seg[ns++] = CopySeg{dst_r, ctx->h_rows[b], n_r * sizeof(nxs_job_row)};
+      if (ns) par_copy(seg, ns);
       out_secs[b] += now() - t1;
     });
   };
-  auto copy_out = [&](int b) -> int { // wait for the helper of set b
+  auto copy_out = [&](int b) -> int { // wait for the helpers of set b
     if (!out_wait[b]) return NXS_OK;
     const double t0 = now();
     if (out_thread[b].joinable()) out_thread[b].join();
+    if (code_thread[b].joinable()) code_thread[b].join();
     t_wait_d2h += now() - t0;
     out_wait[b] = false;
-    if (out_rc[b] != NXS_OK) {
+    if (out_rc[b] != NXS_OK || code_rc[b] != NXS_OK) {
       snprintf(ctx->err, sizeof ctx->err, "copying a slice's results to the caller's buffers failed");
-      const int r = out_rc[b];
-      out_rc[b] = NXS_OK;
+      const int r = out_rc[b] != NXS_OK ? out_rc[b] : code_rc[b];
+      out_rc[b] = code_rc[b] = NXS_OK;
       return r;
     }
     return NXS_OK;
@@ -554,41 +634,49 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
     // where this slice's columns are read from: the caller's buffers, or page-locked copies of them
     const uint64_t *s_key = in->job_key + lo;
     const uint16_t *s_reason = attr ? attr + lo : in->reason_id + lo;
-    const uint8_t *s_kind = attr ? nullptr : in->kind + lo, *s_flags = attr ? nullptr : in->flags + lo,
-                  *s_stage = attr ? nullptr : in->cur_stage + lo;
+    const uint8_t *s_kind = packed ? nullptr : in->kind + lo, *s_flags = packed ? nullptr : in->flags + lo,
+                  *s_stage = packed ? nullptr : in->cur_stage + lo;
+    if (bounce_in || autopack)
+      NXS_CUDA(ctx, cudaEventSynchronize(ctx->e_h2d[b])); // (the upload of the slice before last has long left the set's host staging)
+    if (autopack) { // the four small columns of the slice -> one page-locked u16 column (while the previous slice is on the wire)
+      const double t0 = now();
+      pack_columns(in->kind + lo, in->reason_id + lo, in->flags + lo, in->cur_stage + lo, m, ctx->h_attr[b]);
+      t_in += now() - t0;
+      s_reason = ctx->h_attr[b];
+    }
     if (bounce_in) {
-      NXS_CUDA(ctx, cudaEventSynchronize(ctx->e_h2d[b])); // (the upload of the slice before last has long left the set)
       uint8_t *hb = ctx->h_in[b];
-      CopySeg seg[5] = {{hb, s_key, m * 8}, {hb + cap * 8, s_reason, m * 2}, {hb + cap * 10, s_kind, attr ? 0 : m},
-                        {hb + cap * 11, s_flags, attr ? 0 : m}, {hb + cap * 12, s_stage, attr ? 0 : m}};
+      CopySeg seg[5] = {{hb, s_key, m * 8}, {hb + cap * 8, s_reason, autopack ? 0 : m * 2}, {hb + cap * 10, s_kind, packed ? 0 : m},
+                        {hb + cap * 11, s_flags, packed ? 0 : m}, {hb + cap * 12, s_stage, packed ? 0 : m}};
       const double t0 = now();
       par_copy(seg, 5);
       t_in += now() - t0;
       s_key = reinterpret_cast<const uint64_t *>(hb);
-      s_reason = reinterpret_cast<const uint16_t *>(hb + cap * 8);
+      if (!autopack) s_reason = reinterpret_cast<const uint16_t *>(hb + cap * 8);
       s_kind = hb + cap * 10, s_flags = hb + cap * 11, s_stage = hb + cap * 12;
     }
     // upload (after the previous user of this buffer set has been fully downloaded)
     NXS_CUDA(ctx, cudaStreamWaitEvent(ctx->s_h2d, ctx->e_d2h[b], 0));
     NXS_CUDA(ctx, cudaMemcpyAsync(d_key, s_key, m * 8, cudaMemcpyHostToDevice, ctx->s_h2d));
     NXS_CUDA(ctx, cudaMemcpyAsync(d_reason, s_reason, m * 2, cudaMemcpyHostToDevice, ctx->s_h2d)); // (attr when packed: 10 bytes per record on the wire instead of 13)
-    if (!attr) {
+    if (!packed) {
       NXS_CUDA(ctx, cudaMemcpyAsync(d_kind, s_kind, m, cudaMemcpyHostToDevice, ctx->s_h2d));
       NXS_CUDA(ctx, cudaMemcpyAsync(d_flags, s_flags, m, cudaMemcpyHostToDevice, ctx->s_h2d));
       NXS_CUDA(ctx, cudaMemcpyAsync(d_stage, s_stage, m, cudaMemcpyHostToDevice, ctx->s_h2d));
     }
     NXS_CUDA(ctx, cudaEventRecord(ctx->e_h2d[b], ctx->s_h2d));
+    ctx->wire_h2d += m * (packed ? 10u : 13u);
     // classify
     NXS_CUDA(ctx, cudaStreamWaitEvent(s_comp, ctx->e_h2d[b], 0));
-    if (attr) {
+    if (packed) {
       const unsigned blocks = (unsigned)std::min<uint64_t>((m + 255) / 256, (uint64_t)ctx->num_sms * 16);
       expand_attr_kernel<<<blocks, 256, 0, s_comp>>>(d_reason, m, d_reason, d_kind, d_flags, d_stage);
       NXS_CUDA(ctx, cudaGetLastError());
       ctx->launches += 1;
     }
     nxs_batch d_in{d_kind, d_reason, d_flags, d_stage, d_key, m};
-    nxs_out d_out{out->verdict ? ctx->d_verdict[b] : nullptr, ctx->d_rows[b], ctx->d_njobs + b};
-    rc = launch_classify(ctx, &d_in, &d_out, (uint32_t)lo);
+    nxs_out d_out{out->verdict && !codes ? ctx->d_verdict[b] : nullptr, ctx->d_rows[b], ctx->d_njobs + b};
+    rc = launch_classify(ctx, &d_in, &d_out, (uint32_t)lo, codes ? reinterpret_cast<uint8_t *>(ctx->d_verdict[b]) : nullptr);
     if (rc != NXS_OK) return rc;
     NXS_CUDA(ctx, cudaEventRecord(ctx->e_kernel[b], s_comp));
     // The previous slice's rows go out first (rows land in slice order, and the next upload into its
@@ -598,20 +686,27 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
       if (rc != NXS_OK) return rc;
       start_copy_out(b ^ 1);
     }
-    if (bounce_out) { // the set's previous results must have left its bounce buffers before new ones are queued into them
+    if (helpers) { // the set's previous results must have left its host staging before new ones are queued into it
       rc = copy_out(b);
       if (rc != NXS_OK) return rc;
     }
     NXS_CUDA(ctx, cudaStreamWaitEvent(ctx->s_d2h, ctx->e_kernel[b], 0));
     NXS_CUDA(ctx, cudaMemcpyAsync(ctx->h_njobs + b, ctx->d_njobs + b, 8, cudaMemcpyDeviceToHost, ctx->s_d2h));
     NXS_CUDA(ctx, cudaEventRecord(ctx->e_count[b], ctx->s_d2h));
-    if (out->verdict)
+    if (codes) {
+      NXS_CUDA(ctx, cudaMemcpyAsync(ctx->h_codes[b], ctx->d_verdict[b], m, cudaMemcpyDeviceToHost, ctx->s_d2h));
+      NXS_CUDA(ctx, cudaEventRecord(ctx->e_codes[b], ctx->s_d2h));
+      start_expand(b, lo, m);
+      ctx->wire_d2h += m;
+    } else if (out->verdict) {
       NXS_CUDA(ctx, cudaMemcpyAsync(bounce_out ? ctx->h_verdict[b] : out->verdict + lo, ctx->d_verdict[b], m * 4,
                                     cudaMemcpyDeviceToHost, ctx->s_d2h));
+      ctx->wire_d2h += m * 4;
+    }
     pend_lo[b] = lo;
     pend_n[b] = m;
     pending[b] = true;
-    if (bounce_out) out_wait[b] = true, out_lo[b] = lo, out_n[b] = m;
+    if (helpers) out_wait[b] = true, out_lo[b] = lo, out_n[b] = m;
     lo = hi;
   }
   for (int b = 0; b < 2; ++b) {
@@ -630,8 +725,8 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
   NXS_CUDA(ctx, cudaStreamSynchronize(ctx->s_d2h));
   NXS_CUDA(ctx, cudaStreamSynchronize(s_comp));
   if (verbose)
-    fprintf(stderr, "nxs bounce: copy in %.1f ms, copy out (helper threads) %.1f ms, waiting for job counts %.1f ms, for the helpers %.1f ms\n",
-            t_in * 1e3, (out_secs[0] + out_secs[1]) * 1e3, t_wait_count * 1e3, t_wait_d2h * 1e3);
+    fprintf(stderr, "nxs host path: pack / copy in %.1f ms, copy out (helper threads) %.1f ms, waiting for job counts %.1f ms, for the helpers %.1f ms\n",
+            t_in * 1e3, (out_secs[0] + out_secs[1] + code_secs[0] + code_secs[1]) * 1e3, t_wait_count * 1e3, t_wait_d2h * 1e3);
   *out->n_jobs = rows_done;
   return NXS_OK;
 }
@@ -688,19 +783,14 @@ int nxs_classify_packed(nxs_ctx *ctx, const nxs_batch_packed *in, const nxs_out 
   return classify_host(ctx, &keys, in->attr, out);
 }
 
+void nxs_last_wire_bytes(const nxs_ctx *ctx, uint64_t *h2d, uint64_t *d2h) {
+  if (h2d) *h2d = ctx ? ctx->wire_h2d : 0;
+  if (d2h) *d2h = ctx ? ctx->wire_d2h : 0;
+}
+
 void nxs_pack_columns(const uint8_t *kind, const uint16_t *reason_id, const uint8_t *flags, const uint8_t *cur_stage,
                       uint64_t n, uint16_t *attr) {
-  // (a streaming loop: one thread moves ~1.4e9 records/s, so large batches are split over a few threads)
-  const unsigned hw = std::thread::hardware_concurrency();
-  const unsigned T = (unsigned)std::min<uint64_t>(std::min(16u, hw ? hw : 4u), n / (1u << 20) + 1);
-  auto work = [=](unsigned t) {
-    for (uint64_t i = n * t / T, e = n * (t + 1) / T; i < e; ++i)
-      attr[i] = (uint16_t)NXS_ATTR_PACK(kind[i], reason_id[i], flags[i], cur_stage[i]);
-  };
-  std::vector<std::thread> th;
-  for (unsigned t = 1; t < T; ++t) th.emplace_back(work, t);
-  work(0);
-  for (std::thread &x : th) x.join();
+  pack_columns(kind, reason_id, flags, cur_stage, n, attr);
 }
 
 int nxs_alloc_host(size_t bytes, void **out) {
@@ -803,6 +893,7 @@ extern "C" int nxs_classify_device_noalloc(int device, void *cuda_stream, uint16
   p.stage = in->cur_stage;
   p.key = in->job_key;
   p.verdict = out->verdict;
+  p.verdict_code = nullptr;
   p.rows = out->job_rows;
   p.n_jobs = out->n_jobs;
   p.counters = reinterpret_cast<uint32_t *>(dev->scratch);

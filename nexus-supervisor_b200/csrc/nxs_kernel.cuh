@@ -198,6 +198,28 @@ __host__ __device__ __forceinline__ Summ desc_s_summ(uint64_t s) {
   return Summ{(uint32_t)s, (uint32_t)(s >> 32) & kSummFMask};
 }
 
+// Entry e = arm | 8 * gate class | 32 * finished of the verdict table: the packed verdict of a record that
+// takes switch arm `arm` behind gate `gate` (0 dropped, 1 no checkpoint, 2 finished, 3 applied) plus the four
+// fold bits.  Host and device build the table from the same function.
+__host__ __device__ __forceinline__ uint32_t vt_entry(uint32_t e, const uint16_t *code, uint32_t term_mask) {
+  const uint32_t g = (e >> 3) & 3u, arm = e & 7u;
+  const uint32_t c = code[arm], a = c & 7u, msg = c >> 9;
+  uint32_t v = 0;
+  if (g != 0 && a >= 1 && a <= 4) {
+    const uint32_t fold = VT_HE | (((term_mask >> a) & 1u) ? VT_TERM : 0u) | (a != NXS_ACTION_RUNNING ? VT_FAIL : 0u);
+    if (g == 1) v = a | msg << 9 | 1u << 12 | NXS_ERR_NO_CHECKPOINT << 15 | VT_ERR; // :265-273
+    else if (g == 2) v = a | msg << 9 | 1u << 14 | fold;                             // :276-279
+    else v = applied_verdict(a) | msg << 9 | fold;                                    // :283-370
+  }
+  return v;
+}
+// The per-record verdict as ONE byte: 4 * arm | 32 * gate | 128 * finished — the byte the record pass keeps per
+// record anyway.  The host-pointer path downloads these bytes instead of the 32-bit verdicts when the link is
+// the bottleneck and expands them with this function.
+__host__ __device__ __forceinline__ uint32_t verdict_of_code(uint32_t byte, const uint16_t *code, uint32_t term_mask) {
+  return vt_entry(byte >> 2, code, term_mask) & kVerdictMask;
+}
+
 struct ClassifyParams {
   const uint8_t *kind;
   const uint16_t *reason;
@@ -205,6 +227,7 @@ struct ClassifyParams {
   const uint8_t *stage;
   const uint64_t *key;
   uint32_t *verdict;
+  uint8_t *verdict_code; // instead of `verdict` (which is then null): one byte per record, see verdict_of_code()
   nxs_job_row *rows;
   uint64_t *n_jobs;
   TileDesc *desc;
@@ -683,7 +706,7 @@ __device__ __forceinline__ void sts_u16(uint32_t addr, uint32_t v) {
 // onEvent: guards (:155,:161,:218) and the (kind, reason) switch arms, then superviseAction's order:
 // no checkpoint (:265) -> finished (:276) -> switch (:283).  All of it is table lookups.  On the way
 // the pass leaves what the job pass reads, in place of the columns it consumes (see StageBuf).
-template <int TILE, bool FULL, int STAGES>
+template <int TILE, bool FULL, int STAGES, bool CODES>
 __device__ __forceinline__ void record_pass(const ClassifyParams &p, StageBuf<TILE> &sb, const TileMeta<TILE> &tm,
                                             const Ctl<STAGES> &ctl, uint32_t tile, uint32_t warp, uint32_t lane) {
   static_assert(TILE % (kWorkerWarps * 32 * kRecordGroup) == 0, "a range is a whole number of record groups");
@@ -709,8 +732,9 @@ __device__ __forceinline__ void record_pass(const ClassifyParams &p, StageBuf<TI
   MaskRow *const rows_m = reinterpret_cast<MaskRow *>(sb.flags + r0);
   const bool write_verdict = p.verdict != nullptr; // (the per-record verdicts are optional: the job rows drive the I/O)
   uint32_t *pv = p.verdict + (size_t)start + r0 + lane;
+  uint8_t *pc = p.verdict_code + (size_t)start + r0 + lane;
 #pragma unroll 1
-  for (uint32_t g = 0; g < CPW; g += kRecordGroup, pv += 32 * kRecordGroup) {
+  for (uint32_t g = 0; g < CPW; g += kRecordGroup, pv += 32 * kRecordGroup, pc += 32 * kRecordGroup) {
     uint2 ti[kRecordGroup];
     uint32_t vt[kRecordGroup], off[kRecordGroup];
     // loads and lookups of the whole group first: the stores below land on bytes read here
@@ -726,7 +750,8 @@ __device__ __forceinline__ void record_pass(const ClassifyParams &p, StageBuf<TI
         const uint32_t l2 = ctl.lut2[st * 8u + (fl & 7u)];
         off[u] = arm4 + l2; // 4 * arm | 32 * gate class | 128 * IsFinished(cur_stage): one byte
         vt[u] = *reinterpret_cast<const uint32_t *>(reinterpret_cast<const uint8_t *>(ctl.vt) + off[u]);
-        if (write_verdict) __stcs(pv + 32 * u, vt[u] & kVerdictMask);
+        if (CODES) pc[32 * u] = (uint8_t)off[u]; // (the host expands the byte: verdict_of_code)
+        else if (write_verdict) __stcs(pv + 32 * u, vt[u] & kVerdictMask);
       }
     }
 #pragma unroll
@@ -823,8 +848,13 @@ __device__ __forceinline__ void worker_loop(const ClassifyParams &p, StageBuf<TI
     st_idle += t_b - t_a;
 #endif
     if (warp == 0 && lane == 0) NXS_TRACE_EVENT(p, EV_P1_START, (uint32_t)t);
-    if (full_tile) record_pass<TILE, true, STAGES>(p, sb, tm, ctl, (uint32_t)t, warp, lane);
-    else record_pass<TILE, false, STAGES>(p, sb, tm, ctl, (uint32_t)t, warp, lane);
+    if (p.verdict_code == nullptr) {
+      if (full_tile) record_pass<TILE, true, STAGES, false>(p, sb, tm, ctl, (uint32_t)t, warp, lane);
+      else record_pass<TILE, false, STAGES, false>(p, sb, tm, ctl, (uint32_t)t, warp, lane);
+    } else { // the host-pointer path, link-bound: one byte per record goes out instead of four
+      if (full_tile) record_pass<TILE, true, STAGES, true>(p, sb, tm, ctl, (uint32_t)t, warp, lane);
+      else record_pass<TILE, false, STAGES, true>(p, sb, tm, ctl, (uint32_t)t, warp, lane);
+    }
     __syncwarp();
     // (2) the job pass: the index of the tile's first job row (known since before the tile landed) and its keys
 #ifdef NXS_TRACE_STATS
@@ -1071,16 +1101,8 @@ __global__ void __maxnreg__(NXS_MAXNREG) classify_kernel(const __grid_constant__
   }
   if (tid < 8) ctl.codex[tid] = p.code[tid] ? (p.code[tid] | F_HAS_WIN | F_HAS_APP) : 0u;
   if (tid >= 128 && tid < 192) {
-    const uint32_t e = tid - 128, g = (e >> 3) & 3u, arm = e & 7u;
-    const uint32_t code = p.code[arm], a = code & 7u, msg = code >> 9;
-    uint32_t v = 0;
-    if (g != 0 && a >= 1 && a <= 4) {
-      const uint32_t fold = VT_HE | (((p.term_mask >> a) & 1u) ? VT_TERM : 0u) | (a != NXS_ACTION_RUNNING ? VT_FAIL : 0u);
-      if (g == 1) v = a | msg << 9 | 1u << 12 | NXS_ERR_NO_CHECKPOINT << 15 | VT_ERR; // :265-273
-      else if (g == 2) v = a | msg << 9 | 1u << 14 | fold;                             // :276-279
-      else v = applied_verdict(a) | msg << 9 | fold;                                    // :283-370
-    }
-    ctl.vt[e] = v;
+    const uint32_t e = tid - 128;
+    ctl.vt[e] = vt_entry(e, p.code, p.term_mask);
   }
   __syncthreads(); // the only CTA-wide barrier
 

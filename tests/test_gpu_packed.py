@@ -95,3 +95,24 @@ def test_page_locked_caller_buffers_sliced():
         out_v[:] = 0
         v3, r3 = c.classify_packed(pinned["job_key"], attr, out_verdict=out_v, out_rows=out_r, want_verdict=True)
         util.assert_same(v3, r3, want_v, want_r, "page-locked buffers, packed")
+
+
+@pytest.mark.parametrize("fm", [util.FM_DEFAULT, 0, 0x5A5A])
+def test_multi_slice_batch_over_the_whole_domain(fm):
+    """Batches of more than one slice take the link-lean route inside nxs_classify — the four small columns
+    travel packed, the per-record verdicts come back as one byte each and are expanded on the host — which must
+    not change a bit of the result: every (kind, reason, flags, stage) combination, repeated until the batch
+    needs two slices, jobs of 1 and of 3 records, three finished-masks."""
+    for per_job in (1, 3):
+        base = util.exhaustive_cols(per_job)
+        reps = (9_437_184 + 8192) // len(base["kind"]) + 1
+        cols = {k: np.tile(v, reps) for k, v in base.items()}
+        n = len(cols["kind"])
+        with np.errstate(over="ignore"):  # distinct keys per repetition, runs stay adjacent
+            cols["job_key"] = cols["job_key"] + np.repeat(np.arange(reps, dtype=np.uint64) << np.uint64(40), len(base["kind"]))
+        want_v, want_r = cpu_oracle.classify(cols, fm, threads=cpu_oracle.hardware_threads())
+        with nx.Classifier(device=0, max_records=n, finished_mask=fm) as c:
+            got_v, got_r = c.classify(cols)
+            util.assert_same(got_v, got_r, want_v, want_r, f"two slices fm={fm:#x} per_job={per_job}")
+            up, down = c.last_wire_bytes
+            assert up == 10 * n and down < 2 * n + 16 * len(want_r)

@@ -170,7 +170,9 @@ def test_host_path_slices_on_job_boundaries():
         for _ in range(2):  # the second call reuses the staging buffers and events
             util.assert_same(*c.classify(cols), *cpu_oracle.classify(cols, threads=cpu_oracle.hardware_threads()),
                              "sliced host path")
-        assert c.launches == 2 * 3
+        assert c.launches == 2 * 3 * 2  # per slice: the expansion of the packed small columns, then the classification
+        up, down = c.last_wire_bytes
+        assert up == 10 * n and n + 16 * len(cols['kind']) // 60 <= down < 4 * n + 16 * n  # (verdicts travel as bytes)
 
 
 @pytest.mark.parametrize("n", [(8 << 20) - 1, 8 << 20, (8 << 20) + 1, (9 << 20), (9 << 20) + 1, (16 << 20) + 5])
