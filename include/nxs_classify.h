@@ -213,7 +213,10 @@ int nxs_abi_version(void);
 /* ------------------------------------------------------------- hot path */
 /* onEvent + superviseAction decision for a batch (services/supervisor.go:137-374).
  * Host pointers; copies in, classifies on the GPU, copies verdicts, job rows and
- * the job count back before returning. */
+ * the job count back before returning.  Uses a few host threads of its own for large batches
+ * (copies through page-locked staging when the caller's memory is pageable; for batches of more
+ * than one 8 Mi-record slice, packing of the small columns before the upload and expansion of
+ * the verdicts, which then cross the link as one byte each, after the download). */
 int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out);
 /* The same for a packed batch (host pointers): 10 instead of 13 bytes per record go up, and with
  * out->verdict == NULL only the job rows come down — the layout for callers behind PCIe, who act
@@ -221,7 +224,8 @@ int nxs_classify(nxs_ctx *ctx, const nxs_batch *in, const nxs_out *out);
 int nxs_classify_packed(nxs_ctx *ctx, const nxs_batch_packed *in, const nxs_out *out);
 /* Bytes the last nxs_classify / nxs_classify_packed call of this ctx moved over the host link, as queued
  * (measurement aid: batches of more than one slice upload the four small columns packed into 16 bits —
- * 10 instead of 13 bytes per record — because the kernel reads no more of them). */
+ * 10 instead of 13 bytes per record, the kernel reads no more of them — and download 1 instead of 4 bytes
+ * per verdict). */
 void nxs_last_wire_bytes(const nxs_ctx *ctx, uint64_t *h2d_bytes, uint64_t *d2h_bytes);
 /* Host helper of the flattening layer: attr[i] = NXS_ATTR_PACK(kind[i], reason_id[i], flags[i], cur_stage[i]). */
 void nxs_pack_columns(const uint8_t *kind, const uint16_t *reason_id, const uint8_t *flags,
