@@ -453,10 +453,7 @@ static void par_copy(const CopySeg *seg, int n_seg) {
       off += seg[i].bytes;
     }
   };
-  std::vector<std::thread> th;
-  for (unsigned t = 1; t < T; ++t) th.emplace_back(work, t);
-  work(0);
-  for (std::thread &x : th) x.join();
+  run_parallel(T, work);
 }
 
 // dst[i] = table[codes[i]]: the per-record verdicts of a slice from their one-byte form, over a few host threads.
@@ -466,10 +463,7 @@ static void expand_codes(const uint8_t *codes, uint64_t n, const uint32_t *table
   auto work = [=](unsigned t) {
     for (uint64_t i = n * t / T, e = n * (t + 1) / T; i < e; ++i) dst[i] = table[codes[i]];
   };
-  std::vector<std::thread> th;
-  for (unsigned t = 1; t < T; ++t) th.emplace_back(work, t);
-  work(0);
-  for (std::thread &x : th) x.join();
+  run_parallel(T, work);
 }
 
 // attr[i] = NXS_ATTR_PACK(...) for i in [0, n): a streaming loop (one thread moves ~1.4e9 records/s), split over a
@@ -482,10 +476,7 @@ static void pack_columns(const uint8_t *kind, const uint16_t *reason_id, const u
     for (uint64_t i = n * t / T, e = n * (t + 1) / T; i < e; ++i)
       attr[i] = (uint16_t)NXS_ATTR_PACK(kind[i], reason_id[i], flags[i], cur_stage[i]);
   };
-  std::vector<std::thread> th;
-  for (unsigned t = 1; t < T; ++t) th.emplace_back(work, t);
-  work(0);
-  for (std::thread &x : th) x.join();
+  run_parallel(T, work);
 }
 
 // `attr` != nullptr: the batch is packed (job_key + attr); the four small columns of `in` are unused.
@@ -567,7 +558,7 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
   } join_all{out_thread};
   auto start_expand = [&](int b, uint64_t first, uint64_t count) {
     uint32_t *dst = out->verdict + first;
-    code_thread[b] = std::thread([ctx, b, dst, count, &code_rc, &code_secs, now] {
+    auto body = [ctx, b, dst, count, &code_rc, &code_secs, now] {
       if (cudaSetDevice(ctx->device) != cudaSuccess || cudaEventSynchronize(ctx->e_codes[b]) != cudaSuccess) {
         code_rc[b] = NXS_ERR_CUDA;
         return;
@@ -575,14 +566,19 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
       const double t1 = now();
       expand_codes(ctx->h_codes[b], count, ctx->verdict_of, dst);
       code_secs[b] += now() - t1;
-    });
+    };
+    try {
+      code_thread[b] = std::thread(body);
+    } catch (...) { // no thread to be had: do it here (slower, not wrong)
+      body();
+    }
   };
   auto start_copy_out = [&](int b) {
     if (!out_wait[b] || !bounce_out) return;
     uint32_t *dst_v = out->verdict ? out->verdict + out_lo[b] : nullptr;
     nxs_job_row *dst_r = out->job_rows + out_row0[b];
     const uint64_t n_v = out_n[b], n_r = out_jobs[b];
-    out_thread[b] = std::thread([ctx, b, dst_v, dst_r, n_v, n_r, &out_rc, &out_secs, now, codes, bounce_out] {
+    auto body = [ctx, b, dst_v, dst_r, n_v, n_r, &out_rc, &out_secs, now, codes, bounce_out] {
       if (cudaSetDevice(ctx->device) != cudaSuccess || cudaEventSynchronize(ctx->e_d2h[b]) != cudaSuccess) {
         out_rc[b] = NXS_ERR_CUDA;
         return;
@@ -594,7 +590,12 @@ static int classify_slices(nxs_ctx *ctx, const nxs_batch *in, const uint16_t *at
       if (bounce_out) seg[ns++] = CopySeg{dst_r, ctx->h_rows[b], n_r * sizeof(nxs_job_row)};
       if (ns) par_copy(seg, ns);
       out_secs[b] += now() - t1;
-    });
+    };
+    try {
+      out_thread[b] = std::thread(body);
+    } catch (...) {
+      body();
+    }
   };
   auto copy_out = [&](int b) -> int { // wait for the helpers of set b
     if (!out_wait[b]) return NXS_OK;

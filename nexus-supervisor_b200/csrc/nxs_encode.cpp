@@ -59,11 +59,10 @@ inline uint64_t details_len(const nxs_job_row &r, const uint64_t *msg_offsets, u
 
 } // namespace
 
-extern "C" int nxs_encode_checkpoint_rows(const nxs_job_row *rows, uint64_t n_rows, const uint8_t *msg_heap,
-                                          const uint64_t *msg_offsets, uint64_t n_records,
-                                          const char *const *stage_names, uint8_t *arena, uint64_t arena_capacity,
-                                          uint64_t *offsets, uint32_t *update_row, uint8_t *update_flags,
-                                          uint64_t *n_updates, uint64_t *arena_bytes) {
+static int encode_impl(const nxs_job_row *rows, uint64_t n_rows, const uint8_t *msg_heap, const uint64_t *msg_offsets,
+                       uint64_t n_records, const char *const *stage_names, uint8_t *arena, uint64_t arena_capacity,
+                       uint64_t *offsets, uint32_t *update_row, uint8_t *update_flags, uint64_t *n_updates,
+                       uint64_t *arena_bytes) {
   if ((!rows && n_rows) || !n_updates || !arena_bytes) return NXS_ERR_ARG;
   if (msg_offsets && !msg_heap) return NXS_ERR_ARG;
   const Tables t = build_tables(stage_names);
@@ -71,12 +70,7 @@ extern "C" int nxs_encode_checkpoint_rows(const nxs_job_row *rows, uint64_t n_ro
   const unsigned T = (unsigned)std::min<uint64_t>(hw == 0 ? 4 : hw > 32 ? 32 : hw, (n_rows + 65535) / 65536 + (n_rows == 0));
   std::vector<uint64_t> cnt(T + 1, 0), bytes(T + 1, 0);
   auto range = [&](unsigned k, uint64_t &lo, uint64_t &hi) { lo = n_rows * k / T, hi = n_rows * (k + 1) / T; };
-  auto run = [&](auto &&fn) {
-    std::vector<std::thread> th;
-    for (unsigned k = 1; k < T; ++k) th.emplace_back(fn, k);
-    fn(0u);
-    for (std::thread &x : th) x.join();
-  };
+  auto run = [&](auto &&fn) { nxs::run_parallel(T, fn); };
   // pass 1: how many updates and bytes per slice of the rows
   run([&](unsigned k) {
     uint64_t lo, hi, c = 0, b = 0;
@@ -149,4 +143,17 @@ extern "C" int nxs_encode_checkpoint_rows(const nxs_job_row *rows, uint64_t n_ro
   });
   offsets[3 * cnt[T]] = bytes[T];
   return NXS_OK;
+}
+
+extern "C" int nxs_encode_checkpoint_rows(const nxs_job_row *rows, uint64_t n_rows, const uint8_t *msg_heap,
+                                          const uint64_t *msg_offsets, uint64_t n_records,
+                                          const char *const *stage_names, uint8_t *arena, uint64_t arena_capacity,
+                                          uint64_t *offsets, uint32_t *update_row, uint8_t *update_flags,
+                                          uint64_t *n_updates, uint64_t *arena_bytes) {
+  try {
+    return encode_impl(rows, n_rows, msg_heap, msg_offsets, n_records, stage_names, arena, arena_capacity, offsets,
+                       update_row, update_flags, n_updates, arena_bytes);
+  } catch (...) { // (std::bad_alloc from the string tables: nothing is thrown across the C ABI)
+    return NXS_ERR_NOMEM;
+  }
 }

@@ -1,6 +1,7 @@
 // nxs_host.h — host-only pieces shared by the translation units of the library.
 #pragma once
 #include <cstdint>
+#include <thread>
 
 #include "nxs_classify.h"
 
@@ -15,5 +16,28 @@ inline uint64_t splitmix64(uint64_t x) {
   z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
   z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
   return z ^ (z >> 31);
+}
+
+// fn(0) .. fn(T-1), fn(0) on the calling thread and the others on threads of their own, all finished on
+// return.  A thread that cannot be started (resource limit) costs parallelism, not the call: its share
+// runs on the calling thread, and nothing is thrown — these loops run below a C ABI.
+template <class Fn> inline void run_parallel(unsigned T, Fn &&fn) {
+  constexpr unsigned kMax = 256;
+  std::thread th[kMax];
+  unsigned started = 0;
+  for (unsigned t = 1; t < T; ++t) {
+    bool ok = false;
+    if (started < kMax) {
+      try {
+        th[started] = std::thread([&fn, t] { fn(t); });
+        ok = true;
+        ++started;
+      } catch (...) {
+      }
+    }
+    if (!ok) fn(t);
+  }
+  if (T > 0) fn(0u);
+  for (unsigned i = 0; i < started; ++i) th[i].join();
 }
 } // namespace nxs

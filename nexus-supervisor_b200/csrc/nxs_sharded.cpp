@@ -126,7 +126,12 @@ int nxs_sharded_create(uint32_t n_shards, const int *devices, uint32_t n_devices
   if (!h) return NXS_ERR_NOMEM;
   h->n_shards = n_shards;
   h->max_records = max_records;
-  h->shard.resize(n_shards);
+  try {
+    h->shard.resize(n_shards);
+  } catch (...) {
+    delete h;
+    return NXS_ERR_NOMEM;
+  }
   const unsigned hw = std::thread::hardware_concurrency();
   h->host_threads = hw == 0 ? 4u : hw > 32u ? 32u : hw;
   for (uint32_t s = 0; s < n_shards; ++s) {
@@ -161,7 +166,12 @@ static int classify_on_ctx(void *user, uint32_t shard, const nxs_batch *in, cons
 }
 
 int nxs_classify_sharded(nxs_sharded *h, const nxs_batch *in, const nxs_out *out) {
-  return classify_sharded_impl(h, in, out, classify_on_ctx, h);
+  try {
+    return classify_sharded_impl(h, in, out, classify_on_ctx, h);
+  } catch (...) { // (std::bad_alloc from the bookkeeping vectors: nothing is thrown across the C ABI)
+    if (h) snprintf(h->err, sizeof h->err, "out of host memory");
+    return NXS_ERR_NOMEM;
+  }
 }
 
 // Test hook (not in the public header): the division-free shard map of the host passes, to be compared
@@ -184,7 +194,12 @@ int nxs_internal_sharded_run(uint32_t n_shards, const nxs_batch *in, const nxs_o
   for (ShardBuf &b : h.shard) b.pinned = false;
   h.host_threads = 3; // more chunks than one, fewer than the shards of some tests
   if (const char *e = getenv("NXS_HOOK_THREADS")) h.host_threads = (unsigned)std::max(1, atoi(e)); // (host-pass timing)
-  const int rc = classify_sharded_impl(&h, in, out, classify, user);
+  int rc;
+  try {
+    rc = classify_sharded_impl(&h, in, out, classify, user);
+  } catch (...) {
+    rc = NXS_ERR_NOMEM;
+  }
   for (ShardBuf &b : h.shard) free_bufs(b);
   return rc;
 }
@@ -226,12 +241,7 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
   }
   // per chunk and shard: records and jobs
   std::vector<uint64_t> rec_cnt((size_t)T * G, 0), job_cnt((size_t)T * G, 0);
-  auto parallel = [&](auto &&fn) {
-    std::vector<std::thread> th;
-    for (unsigned t = 1; t < T; ++t) th.emplace_back(fn, t);
-    fn(0u);
-    for (std::thread &x : th) x.join();
-  };
+  auto parallel = [&](auto &&fn) { nxs::run_parallel(T, fn); };
   // The three host passes below visit RECORDS, not jobs: a loop over the few records of a job ends on a
   // branch nobody can predict, and at a few records per job that branch was most of the time.  The shard
   // is recomputed for every record (a hash and a mask or three multiplications), cursors advance by 0 or 1.
@@ -308,7 +318,6 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
   lap("partition (scatter)");
   // ---- classify: one thread per shard, each on its own ctx (and GPU)
   {
-    std::vector<std::thread> th;
     auto run = [&](uint32_t s) {
       ShardBuf &b = h->shard[s];
       b.rc = NXS_OK;
@@ -320,9 +329,7 @@ static int classify_sharded_impl(nxs_sharded *h, const nxs_batch *in, const nxs_
       if (b.rc != NXS_OK) return;
       if (jobs != b.n_jobs) b.rc = NXS_ERR_CUDA;
     };
-    for (uint32_t s = 1; s < G; ++s) th.emplace_back(run, s);
-    run(0);
-    for (std::thread &x : th) x.join();
+    nxs::run_parallel(G, run);
   }
   lap("classify (all shards)");
   for (uint32_t s = 0; s < G; ++s)
