@@ -277,3 +277,24 @@ extern "C" int nxs_foldsim_ranges(const uint8_t *kind, const uint16_t *reason, c
   *n_jobs = n_rows;
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// run_parallel (nxs_host.h), the helper every host loop of the library runs through: every share runs
+// exactly once whatever the number of shares — more than the helper has thread slots for included, which
+// takes the same path as a thread that cannot be started (the share runs on the calling thread).
+#include <atomic>
+extern "C" int nxs_foldsim_run_parallel(unsigned shares, unsigned long long *sum_of_squares) {
+  std::atomic<unsigned> ran{0};
+  std::atomic<unsigned long long> sum{0};
+  std::vector<std::atomic<unsigned char>> seen(shares);
+  for (auto &x : seen) x = 0;
+  nxs::run_parallel(shares, [&](unsigned t) {
+    ran += 1;
+    sum += (unsigned long long)t * t;
+    seen[t] += 1;
+  });
+  for (auto &x : seen)
+    if (x != 1) return -1;
+  *sum_of_squares = sum;
+  return (int)ran.load();
+}

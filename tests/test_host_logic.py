@@ -185,3 +185,16 @@ def test_job_pass_synthetic_stream():
     for workload in (1, 2):
         cols = cpu_oracle.generate(workload, 200_000)
         util.assert_same(*foldsim_ranges(cols, util.FM_DEFAULT, 512), *cpu_oracle.classify(cols), f"workload={workload}")
+
+
+@pytest.mark.parametrize("shares", [0, 1, 2, 7, 32, 256, 257, 300])
+def test_run_parallel_runs_every_share_exactly_once(shares):
+    """The helper behind every host loop of the library (nxs_host.h): each share runs once, also when there
+    are more shares than thread slots — the path a thread that cannot be started takes as well."""
+    sim = C.CDLL(os.path.join(ROOT, "tests", "foldsim", "_build", "libnxs_foldsim.so"))
+    sim.nxs_foldsim_run_parallel.restype = C.c_int
+    sim.nxs_foldsim_run_parallel.argtypes = [C.c_uint, C.POINTER(C.c_ulonglong)]
+    total = C.c_ulonglong(0)
+    assert sim.nxs_foldsim_run_parallel(shares, C.byref(total)) == shares
+    assert total.value == sum(t * t for t in range(shares))
+
