@@ -298,3 +298,28 @@ extern "C" int nxs_foldsim_run_parallel(unsigned shares, unsigned long long *sum
   *sum_of_squares = sum;
   return (int)ran.load();
 }
+
+// ------------------------------------------------------------------------------------------------
+// The per-record decision as the host-pointer path reconstructs it: the one-byte code of a record
+// (4 * arm | 32 * gate | 128 * finished, built here from the product's tables exactly as the kernel's
+// set-up code does) expanded by verdict_of_code() — the function nxs_create fills its 256-entry table from.
+#include "nxs_kernel.cuh"
+extern "C" void nxs_foldsim_verdict_via_code(const uint8_t *kind, const uint16_t *reason, const uint8_t *flags,
+                                             const uint8_t *stage, uint64_t n, uint32_t finished_mask, uint8_t *code_out,
+                                             uint32_t *verdict_out) {
+  uint8_t lut[128];
+  uint16_t code[8];
+  nxs::nxs_build_lut(lut, code);
+  uint32_t term_mask = 0;
+  for (uint32_t a = 1; a <= 4; ++a)
+    if ((finished_mask >> nxs::new_stage_of(a)) & 1u) term_mask |= 1u << a;
+  for (uint64_t i = 0; i < n; ++i) {
+    const uint32_t k = kind[i] < 3 ? kind[i] : 3, r = reason[i] < 32 ? reason[i] : 32;
+    const uint32_t arm = r < 32 ? lut[k * 32 + r] : 0; // (the kernel's staged table has a zero column 32)
+    const uint32_t fl = flags[i] & 7u, st = stage[i] & 15u, fin = (finished_mask >> st) & 1u;
+    const uint32_t gate = (fl & 3u) != 3u ? 0u : !(fl & NXS_FLAG_CHECKPOINT) ? 1u : fin ? 2u : 3u;
+    const uint32_t byte = 4u * arm | 32u * gate | 128u * fin;
+    code_out[i] = (uint8_t)byte;
+    verdict_out[i] = nxs::verdict_of_code(byte, code, term_mask);
+  }
+}

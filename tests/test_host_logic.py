@@ -198,3 +198,23 @@ def test_run_parallel_runs_every_share_exactly_once(shares):
     assert sim.nxs_foldsim_run_parallel(shares, C.byref(total)) == shares
     assert total.value == sum(t * t for t in range(shares))
 
+
+@pytest.mark.parametrize("fm", util.MASKS)
+def test_verdict_bytes_expand_to_the_oracle_verdicts(fm):
+    """Batches of more than one slice bring the per-record verdicts back as one byte each; the host expands
+    them with verdict_of_code().  Over the whole input domain: the byte built from the product's tables, then
+    expanded, is the oracle's per-record verdict — and the byte is a multiple of four below 256."""
+    sim = C.CDLL(os.path.join(ROOT, "tests", "foldsim", "_build", "libnxs_foldsim.so"))
+    cols = util.exhaustive_cols(1)
+    n = len(cols["kind"])
+    code = np.zeros(n, np.uint8)
+    got = np.zeros(n, np.uint32)
+    sim.nxs_foldsim_verdict_via_code.restype = None
+    sim.nxs_foldsim_verdict_via_code(C.c_void_p(cols["kind"].ctypes.data), C.c_void_p(cols["reason_id"].ctypes.data),
+                                     C.c_void_p(cols["flags"].ctypes.data), C.c_void_p(cols["cur_stage"].ctypes.data),
+                                     C.c_uint64(n), C.c_uint32(fm), C.c_void_p(code.ctypes.data), C.c_void_p(got.ctypes.data))
+    want, _ = cpu_oracle.classify(cols, fm)
+    bad = np.nonzero(got != want)[0]
+    assert bad.size == 0, (bad[:5], got[bad[:5]], want[bad[:5]])
+    assert not (code & 3).any()
+
